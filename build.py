@@ -1,0 +1,64 @@
+#!/usr/bin/env python
+"""Builds the in-tree native artefacts:
+  norm_b200/libnorm_cuda.so   nvcc, sm_100a only (the product)
+  oracle/libnorm_oracle.so    gcc (the CPU checker; test infrastructure)
+Both .so files are git-ignored and travel to the GPU box with the gpurun snapshot.
+"""
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(ROOT, "norm_b200", "csrc")
+LIB = os.path.join(ROOT, "norm_b200", "libnorm_cuda.so")
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-O3", "-std=c++17", "-lineinfo",
+    "-fmad=false",                      # no silent FMA contraction: every fma in the kernels is explicit
+    "-Xcompiler", "-fPIC,-O2,-ffp-contract=off,-Wall",
+    "-Xptxas", "-v",
+    "-shared", "-cudart", "static",
+]
+
+
+def _stale(target, sources):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources)
+
+
+def build_cuda(force=False, verbose=False):
+    srcs = [os.path.join(CSRC, n) for n in sorted(os.listdir(CSRC))]
+    srcs += [os.path.join(ROOT, "include", "norm_cuda.h"), os.path.abspath(__file__)]
+    if not (force or _stale(LIB, srcs)):
+        return LIB
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    env = dict(os.environ)
+    env.pop("CC", None)
+    env.pop("CXX", None)
+    cmd = [nvcc, "-ccbin", "/usr/bin/g++"] + NVCC_FLAGS + ["-o", LIB, os.path.join(CSRC, "norm_cuda.cu")]
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env)
+    log = os.path.join(ROOT, "norm_b200", "build.log")
+    with open(log, "w") as f:
+        f.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
+    if verbose or r.returncode != 0:
+        sys.stderr.write(r.stdout + r.stderr)
+    if r.returncode != 0:
+        raise RuntimeError("nvcc failed, see " + log)
+    return LIB
+
+
+def build_oracle(force=False):
+    args = ["make", "-C", os.path.join(ROOT, "oracle"), "-s"]
+    if force:
+        args.append("-B")
+    subprocess.check_call(args)
+    return os.path.join(ROOT, "oracle", "libnorm_oracle.so")
+
+
+if __name__ == "__main__":
+    force = "--force" in sys.argv
+    print(build_cuda(force=force, verbose="-v" in sys.argv))
+    print(build_oracle(force=force))

@@ -1,0 +1,246 @@
+/*
+ * norm_cuda.h -- C ABI of libnorm_cuda.so: a B200 (sm_100a) CUDA backend for the
+ * data-parallel image-effect path of friendlymatthew/norm.
+ *
+ * The reference crate exports no FFI for this path (it is a cdylib + rlib with no
+ * #[no_mangle] symbols, Cargo.toml:42-43); the seam this library replaces is the Rust-level
+ * one between `renderer::app_state` and wgpu.  Each entry point below cites the reference
+ * interface it stands in for (paths relative to the reference repository root).
+ * INTEGRATION.md shows the `extern "C"` block + safe wrapper a norm maintainer would add as
+ * `src/renderer/cuda_backend.rs`.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++ / torch types cross this boundary;
+ *   - every function returns a norm_status; nothing throws or aborts across the ABI
+ *     (the reference's release profile is panic = "abort", Cargo.toml:47);
+ *   - the caller owns every host buffer; the library owns device and pinned memory behind
+ *     opaque handles with explicit *_destroy / *_free;
+ *   - a context is bound to ONE device and is thread-compatible (one thread at a time);
+ *     all work of a context is ordered on its stream; calls are synchronous unless named
+ *     *_async (finish those with norm_cuda_sync);
+ *   - pixels are RGBA8, row-major, top row first; device images are pitched (pitch % 16 == 0).
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails with
+ *     NORM_E_CUDA.
+ */
+#ifndef NORM_CUDA_H
+#define NORM_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NORM_CUDA_ABI_VERSION 1
+
+typedef int32_t norm_status;
+enum {
+    NORM_OK = 0,
+    NORM_E_INVALID_ARG = 1,  /* `ensure!` / `bail!` class of errors (decoder.rs:30-33, ssim.rs:92-95) */
+    NORM_E_UNSUPPORTED = 2,  /* where the reference hits unimplemented!/todo! (grammar.rs:119,153,195) */
+    NORM_E_CUDA = 3,
+    NORM_E_NCCL = 4,
+    NORM_E_OOM = 5,
+    NORM_E_DIM_MISMATCH = 6  /* ssim.rs:92-95 "identical dimensions" */
+};
+
+/* Effect parameters.  Field-for-field copy of `FeatureUniform`
+ * (src/renderer/feature_uniform.rs:1-17; WGSL mirror image_shader.wgsl:2-15): 112 bytes. */
+typedef struct NormFeatureUniform {
+    uint32_t grayscale;      /* 1 = on (feature_uniform.rs:40-42)                       */
+    uint32_t invert;
+    uint32_t gamma;          /* raw gAMA * 1e5, 0 = pass-through (app_state.rs:65)      */
+    uint32_t blur;
+    uint32_t blur_radius;    /* UI range 3..39 step 2, default 21 (feature_uniform.rs:66-84); accepted 1..63 */
+    uint32_t width;          /* must equal the image width  (app_state.rs:65,678-682)   */
+    uint32_t height;         /* must equal the image height                             */
+    uint32_t sharpen;
+    uint32_t sharpen_factor; /* UI range 1..40, default 16 (feature_uniform.rs:88-106)  */
+    uint32_t edge_detect;
+    uint8_t _padding_1[8];
+    float transform[4][4];   /* FlipX / FlipY matrix (feature_uniform.rs:143-175)       */
+} NormFeatureUniform;
+
+#define NORM_MAX_BLUR_RADIUS 63u
+
+/* flags for the effect entry points */
+enum {
+    NORM_CS_REFERENCE = 0u, /* input is sRGB-encoded: decoded at first load as Rgba8UnormSrgb does
+                               (texture.rs:36); intermediates are linear unorm8 (gpu_state.rs:608) */
+    NORM_CS_RAW = 1u        /* bytes/255 throughout (synthetic data) */
+};
+
+/* Decoded PNG as the reference's `Png` holds it (src/png/grammar.rs:65-70): header fields,
+ * raw gAMA, and `pixel_buffer` = unfiltered scanlines without filter bytes, raster order,
+ * row stride ceil(width*channels*bit_depth/8).  plte / trns carry the PLTE and tRNS chunk
+ * bodies the reference drops (decoder.rs:64-76,204-209); NULL/0 when absent. */
+typedef struct NormPngDesc {
+    uint32_t width, height;
+    uint8_t bit_depth;   /* 1,2,4,8,16 */
+    uint8_t color_type;  /* 0,2,3,4,6 (src/image/grammar.rs:10-17) */
+    uint8_t _reserved[2];
+    uint32_t gamma;
+    const uint8_t *pixels;
+    size_t len;
+    const uint8_t *plte;
+    int32_t n_plte;      /* entries (3 bytes each), <= 256 */
+    const uint8_t *trns;
+    int32_t n_trns;      /* bytes, <= 256 */
+} NormPngDesc;
+
+enum {
+    NORM_EXPAND_COMPAT = 0, /* bit-exact `Png::rgba8()` (grammar.rs:123-155): 8-bit ct 0/2/4/6, alpha 0 for opaque types */
+    NORM_EXPAND_SPEC = 1    /* every PngSuite colour type / depth, PLTE + tRNS, 16->8 via (v+128)/257, opaque alpha 255 */
+};
+
+typedef struct norm_ctx norm_ctx;
+typedef struct norm_img norm_img; /* `frames` device-resident RGBA8 images of equal size */
+
+/* ---- library / context ------------------------------------------------------------- */
+
+/* ABI version of the loaded library. */
+int32_t norm_cuda_abi_version(void);
+/* Static description of a status code. */
+const char *norm_cuda_status_string(norm_status s);
+
+/* Replaces GpuResourceAllocator::new (src/renderer/gpu_state.rs:49-132): binds a context to
+ * CUDA device `device` and creates its streams.  Fails with NORM_E_CUDA if no device. */
+norm_status norm_cuda_create(int32_t device, norm_ctx **out);
+/* As above but all work is issued on the caller's stream (a cudaStream_t cast to void*),
+ * so the caller's own CUDA events bracket the kernels. */
+norm_status norm_cuda_create_on_stream(int32_t device, void *cuda_stream, norm_ctx **out);
+void norm_cuda_destroy(norm_ctx *ctx);
+/* Last error text of this context ("" if none); valid until the next call on the context.
+ * ctx may be NULL: returns the text of the last failed norm_cuda_create on this thread. */
+const char *norm_cuda_last_error(const norm_ctx *ctx);
+/* Blocks until all work issued on the context has finished (queue.submit + wait analogue,
+ * gpu_state.rs:593-595). */
+norm_status norm_cuda_sync(norm_ctx *ctx);
+/* Number of kernels this context has launched since creation. */
+uint64_t norm_cuda_launch_count(const norm_ctx *ctx);
+/* Device facts for reports: SM count, bytes of device memory, name (<= 127 chars). */
+norm_status norm_cuda_device_info(const norm_ctx *ctx, int32_t *sm_count, size_t *total_mem,
+                                  char *name, size_t name_cap);
+
+/* GPU timing on the context's stream: start/stop bracket a region with CUDA events;
+ * elapsed_ms synchronises on the stop event. */
+norm_status norm_cuda_timer_start(norm_ctx *ctx);
+norm_status norm_cuda_timer_stop(norm_ctx *ctx);
+norm_status norm_cuda_timer_elapsed_ms(norm_ctx *ctx, float *ms);
+
+/* ---- image buffers ----------------------------------------------------------------- */
+
+/* Replaces create_storage_texture / Texture::from_image's device allocation
+ * (gpu_state.rs:597-623, texture.rs:37-46): `frames` pitched RGBA8 images. */
+norm_status norm_cuda_image_create(norm_ctx *ctx, uint32_t width, uint32_t height, uint32_t frames,
+                                   norm_img **out);
+/* Wraps caller-owned device memory (not freed by image_destroy).  pitch % 16 == 0,
+ * frame_stride >= pitch*height and % 16 == 0, ptr 16-byte aligned. */
+norm_status norm_cuda_image_wrap(norm_ctx *ctx, void *device_ptr, uint32_t width, uint32_t height,
+                                 uint32_t frames, size_t pitch, size_t frame_stride, norm_img **out);
+void norm_cuda_image_destroy(norm_ctx *ctx, norm_img *img);
+norm_status norm_cuda_image_info(const norm_img *img, uint32_t *width, uint32_t *height,
+                                 uint32_t *frames, size_t *pitch, size_t *frame_stride,
+                                 void **device_ptr);
+
+/* Replaces queue.write_texture in Texture::from_image (src/renderer/texture.rs:48-62):
+ * copies `nframes` tightly-or-strided host RGBA8 frames (host_pitch bytes per row, frames
+ * back to back) into frames [frame0, frame0+nframes).  Batched: one 2-D copy per call when
+ * rows are contiguous.  Pinned host memory (norm_cuda_host_alloc) makes it asynchronous. */
+norm_status norm_cuda_upload(norm_ctx *ctx, norm_img *img, uint32_t frame0, uint32_t nframes,
+                             const uint8_t *host_rgba8, size_t host_pitch);
+/* The "RGBA8 buffer out" half of the boundary (the reference never reads back,
+ * app_state.rs:567-661; this is new). */
+norm_status norm_cuda_download(norm_ctx *ctx, const norm_img *img, uint32_t frame0, uint32_t nframes,
+                               uint8_t *host_rgba8, size_t host_pitch);
+
+/* Pinned host memory for upload / download / *_host entry points. */
+norm_status norm_cuda_host_alloc(norm_ctx *ctx, size_t bytes, void **out);
+void norm_cuda_host_free(norm_ctx *ctx, void *p);
+
+/* ---- pixel expansion ---------------------------------------------------------------- */
+
+/* Replaces `ImageExt::rgba8()` for `Png` (src/png/grammar.rs:123-155): uploads the packed
+ * scanlines and expands them on the GPU into frame `frame` of `out` (width/height must
+ * match).  NORM_E_UNSUPPORTED in compat mode for inputs the reference cannot expand. */
+norm_status norm_cuda_expand_rgba8(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, norm_img *out,
+                                   uint32_t frame);
+/* Same, result copied to a host buffer of 4*width*height bytes (the Cow<[u8]> the
+ * reference returns). */
+norm_status norm_cuda_expand_rgba8_host(norm_ctx *ctx, const NormPngDesc *png, int32_t mode,
+                                        uint8_t *out_rgba8);
+
+/* ---- effects ------------------------------------------------------------------------ */
+
+/* One frame of the reference renderer, headless: EffectPipeline::execute
+ * (src/renderer/effect_pipeline.rs:39-51) over the effects wired in app_state.rs:95-125
+ * (gamma always; grayscale; invert) followed by the ONE fragment effect fs_main selects,
+ * priority blur > sharpen > edge_detect (image_shader.wgsl:158-174).  Applied to every
+ * frame of `in`; `out` must have the same geometry and may not alias `in`. */
+norm_status norm_cuda_effects(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags,
+                              const norm_img *in, norm_img *out);
+
+/* The chained path of BASELINE.json: front (gamma/grayscale/invert) -> blur -> sharpen ->
+ * edge_detect, every enabled stage reading and writing RGBA8 as the reference's rgba8unorm
+ * storage textures do (gpu_state.rs:608), then SSIM(result, in) per frame
+ * (Png::compute_sim, src/png/ssim.rs:91-106).  ssim: host array of `frames` doubles or NULL. */
+norm_status norm_cuda_chain(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags,
+                            const norm_img *in, norm_img *out, double *ssim);
+/* As norm_cuda_chain but returns without waiting; ssim_dev (device array of `frames` doubles,
+ * may be NULL) receives the SSIM values on the context's stream. */
+norm_status norm_cuda_chain_async(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags,
+                                  const norm_img *in, norm_img *out, double *ssim_dev);
+
+/* Host-buffer form of norm_cuda_chain: `frames` RGBA8 frames in host memory in, RGBA8 out
+ * (tightly packed, 4*width bytes per row).  Uploads, runs and downloads in overlapping
+ * chunks on the context's copy streams.  Use pinned buffers for full PCIe speed. */
+norm_status norm_cuda_chain_host(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags,
+                                 const uint8_t *in_rgba8, uint8_t *out_rgba8, uint32_t frames,
+                                 double *ssim);
+
+/* Single stages, for callers that compose their own pipeline (EffectPipelineBuilder::
+ * add_effect, effect_pipeline.rs:92-123) and for per-stage parity tests. */
+/* gamma_correct_compute.wgsl:15-42 + grayscale_compute.wgsl:11-29 + invert_compute.wgsl:11-33 */
+norm_status norm_cuda_front(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags,
+                            const norm_img *in, norm_img *out);
+/* gaussian_blur, image_shader.wgsl:83-103 */
+norm_status norm_cuda_blur(norm_ctx *ctx, uint32_t radius, const norm_img *in, norm_img *out);
+/* detect_edge, image_shader.wgsl:132-156 */
+norm_status norm_cuda_sobel(norm_ctx *ctx, const norm_img *in, norm_img *out);
+/* sharpen, image_shader.wgsl:120-129 */
+norm_status norm_cuda_sharpen(norm_ctx *ctx, uint32_t factor, const norm_img *in, norm_img *out);
+
+/* ---- SSIM --------------------------------------------------------------------------- */
+
+/* Replaces Png::compute_sim (src/png/ssim.rs:91-106) on expanded RGBA8 images (RGBA luma
+ * branch, ssim.rs:65-81): one global-window SSIM per frame, a[i] against b[i].
+ * NORM_E_DIM_MISMATCH if geometries differ (ssim.rs:92-95).  ssim: `frames` doubles. */
+norm_status norm_cuda_ssim(norm_ctx *ctx, const norm_img *a, const norm_img *b, double *ssim);
+/* The five raw moments per frame {sum x, sum y, sum x^2, sum y^2, sum xy} of the f32 lumas,
+ * accumulated in f64 -- what a multi-GPU caller all-reduces before finalising.
+ * moments: host array of 5*frames doubles. */
+norm_status norm_cuda_ssim_moments(norm_ctx *ctx, const norm_img *a, const norm_img *b, double *moments);
+/* Host-only: SSIM from (all-reduced) moments over npix pixels (ssim.rs:127-183 in f64). */
+double norm_ssim_from_moments(const double moments[5], double npix);
+
+/* ---- host-only planning helpers (usable without a GPU) ------------------------------ */
+
+/* Normalised 1-D taps of the separable blur and the texel offset of tap 0
+ * (image_shader.wgsl:81-103 under the floor convention). */
+norm_status norm_blur_taps(uint32_t radius, float *taps, int32_t *dmin);
+/* 256-entry front table: sRGB decode at load + gamma pass + unorm8 store. */
+norm_status norm_front_lut(uint32_t flags, uint32_t gamma, uint8_t lut[256]);
+/* Row-band plan for one giant image over `nranks` GPUs: rank `rank` owns rows
+ * [*row0, *row0 + *rows) and needs *halo_up / *halo_down source rows from its neighbours
+ * for the enabled stencil stages of `f`. */
+norm_status norm_plan_band(const NormFeatureUniform *f, uint32_t height, int32_t nranks, int32_t rank,
+                           uint32_t *row0, uint32_t *rows, uint32_t *halo_up, uint32_t *halo_down);
+/* Frame-shard plan: rank owns frames [*frame0, *frame0 + *nframes) of `frames`. */
+norm_status norm_plan_frames(uint32_t frames, int32_t nranks, int32_t rank, uint32_t *frame0,
+                             uint32_t *nframes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NORM_CUDA_H */

@@ -1,0 +1,414 @@
+"""Host-side mirror of the reference's effect API over the C ABI.
+
+The reference is compiled Rust; no Rust toolchain exists in this image, so the host layer a
+norm user would touch is mirrored here with the reference's names, argument meaning and
+error behaviour (INTEGRATION.md holds the Rust binding a maintainer would add):
+
+  FeatureUniform   src/renderer/feature_uniform.rs
+  Png / ImageExt   src/png/grammar.rs:65-198, src/image/grammar.rs:48-68
+  Texture          src/renderer/texture.rs:22-80
+  EffectPipeline   src/renderer/effect_pipeline.rs:8-132
+  compute_sim      src/png/ssim.rs:91-106
+
+Everything that computes goes through libnorm_cuda.so; numpy is used only to hold host bytes.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import (NORM_CS_RAW, NORM_CS_REFERENCE, NORM_EXPAND_COMPAT, NORM_EXPAND_SPEC, NORM_OK,
+                   NormFeatureUniform, NormPngDesc)
+
+
+class NormError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__(f"[{_lib.load().norm_cuda_status_string(status).decode()}] {message}")
+        self.status = status
+
+
+class FeatureUniform:
+    """feature_uniform.rs: same fields, defaults, toggles and clamps."""
+    DEFAULT_BLUR_RADIUS, MAX_BLUR_RADIUS, MIN_BLUR_RADIUS = 21, 39, 3
+    DEFAULT_SHARPEN_FACTOR, MAX_SHARPEN_FACTOR, MIN_SHARPEN_FACTOR = 16, 40, 1
+
+    def __init__(self, width, height, gamma=0):  # feature_uniform.rs:20-36 `new`
+        r = NormFeatureUniform()
+        r.width, r.height, r.gamma = width, height, gamma
+        r.blur_radius, r.sharpen_factor = self.DEFAULT_BLUR_RADIUS, self.DEFAULT_SHARPEN_FACTOR
+        for i in range(4):
+            r.transform[i][i] = 1.0
+        self.raw = r
+
+    # predicates compare with 1 exactly, as the reference does (feature_uniform.rs:40-42)
+    def grayscale(self): return self.raw.grayscale == 1
+    def invert(self): return self.raw.invert == 1
+    def blur(self): return self.raw.blur == 1
+    def sharpen(self): return self.raw.sharpen == 1
+    def edge_detect(self): return self.raw.edge_detect == 1
+    def gamma(self): return self.raw.gamma
+
+    def toggle_grayscale(self): self.raw.grayscale = int(not self.grayscale())
+    def toggle_invert(self): self.raw.invert = int(not self.invert())
+    def toggle_blur(self): self.raw.blur = int(not self.blur())
+    def toggle_sharpen(self): self.raw.sharpen = int(not self.sharpen())
+    def toggle_edge_detect(self): self.raw.edge_detect = int(not self.edge_detect())
+
+    def increase_blur_radius(self):  # feature_uniform.rs:76-78
+        self.raw.blur_radius = min(self.raw.blur_radius + 2, self.MAX_BLUR_RADIUS)
+
+    def decrease_blur_radius(self):  # feature_uniform.rs:80-82
+        self.raw.blur_radius = max(self.raw.blur_radius - 2, self.MIN_BLUR_RADIUS)
+
+    def increase_sharpen_factor(self):
+        self.raw.sharpen_factor = min(self.raw.sharpen_factor + 1, self.MAX_SHARPEN_FACTOR)
+
+    def decrease_sharpen_factor(self):
+        self.raw.sharpen_factor = max(self.raw.sharpen_factor - 1, self.MIN_SHARPEN_FACTOR)
+
+    def update_window_dimensions(self, width, height):
+        self.raw.width, self.raw.height = width, height
+
+    def apply_transform(self, action):  # feature_uniform.rs:161-175; action in {"FlipX", "FlipY"}
+        d = {"FlipX": (0, 0), "FlipY": (1, 1)}[action]
+        self.raw.transform[d[0]][d[1]] *= -1.0
+
+    def copy(self):
+        f = FeatureUniform(self.raw.width, self.raw.height, self.raw.gamma)
+        C.memmove(C.byref(f.raw), C.byref(self.raw), C.sizeof(NormFeatureUniform))
+        return f
+
+
+class Png:
+    """Decoded image as the reference holds it (grammar.rs:65-70) + PLTE/tRNS bodies."""
+
+    def __init__(self, width, height, bit_depth, color_type, pixel_buffer, gamma=0, plte=None, trns=None):
+        self.width, self.height = int(width), int(height)
+        self.bit_depth, self.color_type, self._gamma = int(bit_depth), int(color_type), int(gamma)
+        self.pixel_buffer = np.ascontiguousarray(np.frombuffer(bytes(pixel_buffer), np.uint8)
+                                                 if not isinstance(pixel_buffer, np.ndarray) else pixel_buffer,
+                                                 dtype=np.uint8).reshape(-1)
+        self.plte = None if plte is None or len(plte) == 0 else np.ascontiguousarray(plte, np.uint8).reshape(-1)
+        self.trns = None if trns is None or len(trns) == 0 else np.ascontiguousarray(trns, np.uint8).reshape(-1)
+
+    def dimensions(self): return (self.width, self.height)
+    def gamma(self): return self._gamma
+
+    def desc(self):
+        d = NormPngDesc()
+        d.width, d.height, d.bit_depth, d.color_type, d.gamma = (self.width, self.height, self.bit_depth,
+                                                                 self.color_type, self._gamma)
+        d.pixels, d.len = self.pixel_buffer.ctypes.data, self.pixel_buffer.size
+        if self.plte is not None:
+            d.plte, d.n_plte = self.plte.ctypes.data, self.plte.size // 3
+        if self.trns is not None:
+            d.trns, d.n_trns = self.trns.ctypes.data, self.trns.size
+        return d
+
+    def rgba8(self, ctx, mode=NORM_EXPAND_COMPAT):
+        """ImageExt::rgba8 (grammar.rs:123-155), computed on the GPU."""
+        return ctx.expand_rgba8_host(self, mode)
+
+    def compute_sim(self, reference_image, ctx, mode=NORM_EXPAND_COMPAT):
+        """Png::compute_sim (ssim.rs:91-106): `self` is the test image."""
+        if self.dimensions() != reference_image.dimensions():
+            raise NormError(_lib.NORM_E_DIM_MISMATCH,
+                            "Expect reference and test images to have identical dimensions.")
+        a, b = Texture.from_image(ctx, self, mode), Texture.from_image(ctx, reference_image, mode)
+        try:
+            return float(ctx.ssim(a.image, b.image)[0])
+        finally:
+            a.destroy(), b.destroy()
+
+
+class DeviceImage:
+    """`frames` pitched RGBA8 frames in HBM (norm_img)."""
+
+    def __init__(self, ctx, handle):
+        self.ctx, self.handle = ctx, handle
+        w, h, n, pitch, fs, ptr = C.c_uint32(), C.c_uint32(), C.c_uint32(), C.c_size_t(), C.c_size_t(), C.c_void_p()
+        ctx._ok(ctx.lib.norm_cuda_image_info(handle, w, h, n, pitch, fs, C.byref(ptr)))
+        self.width, self.height, self.frames = w.value, h.value, n.value
+        self.pitch, self.frame_stride, self.device_ptr = pitch.value, fs.value, ptr.value
+
+    @property
+    def nbytes(self): return self.frame_stride * self.frames
+
+    def upload(self, host, frame0=0):
+        host = np.ascontiguousarray(host, np.uint8)
+        n = host.size // (self.width * self.height * 4)
+        assert host.size == n * self.width * self.height * 4
+        self.ctx._ok(self.ctx.lib.norm_cuda_upload(self.ctx.h, self.handle, frame0, n, host.ctypes.data, 0))
+        return self
+
+    def download(self, frame0=0, nframes=None):
+        n = self.frames - frame0 if nframes is None else nframes
+        out = np.empty((n, self.height, self.width, 4), np.uint8)
+        self.ctx._ok(self.ctx.lib.norm_cuda_download(self.ctx.h, self.handle, frame0, n, out.ctypes.data, 0))
+        return out
+
+    def destroy(self):
+        if self.handle:
+            self.ctx.lib.norm_cuda_image_destroy(self.ctx.h, self.handle)
+            self.handle = None
+
+
+class Context:
+    """One CUDA device + streams (stands where GpuResourceAllocator does, gpu_state.rs:49-132)."""
+
+    def __init__(self, device=0, stream=None):
+        self.lib = _lib.load()
+        h = C.c_void_p()
+        if stream is None:
+            st = self.lib.norm_cuda_create(device, C.byref(h))
+        else:
+            st = self.lib.norm_cuda_create_on_stream(device, C.c_void_p(stream), C.byref(h))
+        if st != NORM_OK:
+            raise NormError(st, self.lib.norm_cuda_last_error(None).decode())
+        self.h, self.device = h, device
+
+    def _ok(self, st):
+        if st != NORM_OK:
+            raise NormError(st, self.lib.norm_cuda_last_error(self.h).decode())
+
+    def close(self):
+        if self.h:
+            self.lib.norm_cuda_destroy(self.h)
+            self.h = None
+
+    def __enter__(self): return self
+    def __exit__(self, *a): self.close()
+
+    # -- facts / timing
+    def device_info(self):
+        sm, mem, name = C.c_int32(), C.c_size_t(), C.create_string_buffer(128)
+        self._ok(self.lib.norm_cuda_device_info(self.h, sm, mem, name, 128))
+        return {"sm_count": sm.value, "total_mem": mem.value, "name": name.value.decode()}
+
+    def launch_count(self): return int(self.lib.norm_cuda_launch_count(self.h))
+    def sync(self): self._ok(self.lib.norm_cuda_sync(self.h))
+    def timer_start(self): self._ok(self.lib.norm_cuda_timer_start(self.h))
+    def timer_stop(self): self._ok(self.lib.norm_cuda_timer_stop(self.h))
+
+    def timer_elapsed_ms(self):
+        ms = C.c_float()
+        self._ok(self.lib.norm_cuda_timer_elapsed_ms(self.h, ms))
+        return ms.value
+
+    # -- buffers
+    def image_create(self, width, height, frames=1):
+        h = C.c_void_p()
+        self._ok(self.lib.norm_cuda_image_create(self.h, width, height, frames, C.byref(h)))
+        return DeviceImage(self, h)
+
+    def image_wrap(self, device_ptr, width, height, frames, pitch, frame_stride):
+        h = C.c_void_p()
+        self._ok(self.lib.norm_cuda_image_wrap(self.h, C.c_void_p(device_ptr), width, height, frames, pitch,
+                                               frame_stride, C.byref(h)))
+        return DeviceImage(self, h)
+
+    def image_from_host(self, host):
+        host = np.ascontiguousarray(host, np.uint8)
+        if host.ndim == 3:
+            host = host[None]
+        n, hgt, wid, c = host.shape
+        assert c == 4
+        return self.image_create(wid, hgt, n).upload(host)
+
+    def host_alloc(self, nbytes):
+        """Pinned host buffer as a numpy uint8 array (free with host_free)."""
+        p = C.c_void_p()
+        self._ok(self.lib.norm_cuda_host_alloc(self.h, nbytes, C.byref(p)))
+        arr = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(nbytes,))
+        return arr, p
+
+    def host_free(self, p): self.lib.norm_cuda_host_free(self.h, p)
+
+    # -- expansion
+    def expand_rgba8(self, png, mode, out, frame=0):
+        d = png.desc()
+        self._ok(self.lib.norm_cuda_expand_rgba8(self.h, C.byref(d), mode, out.handle, frame))
+
+    def expand_rgba8_host(self, png, mode):
+        out = np.empty((png.height, png.width, 4), np.uint8)
+        d = png.desc()
+        self._ok(self.lib.norm_cuda_expand_rgba8_host(self.h, C.byref(d), mode, out.ctypes.data))
+        return out
+
+    # -- effects
+    @staticmethod
+    def _raw(f): return C.byref(f.raw if isinstance(f, FeatureUniform) else f)
+
+    def effects(self, f, src, dst, flags=NORM_CS_REFERENCE):
+        self._ok(self.lib.norm_cuda_effects(self.h, self._raw(f), flags, src.handle, dst.handle))
+
+    def chain(self, f, src, dst, flags=NORM_CS_REFERENCE, want_ssim=True):
+        s = np.zeros(src.frames, np.float64) if want_ssim else None
+        self._ok(self.lib.norm_cuda_chain(self.h, self._raw(f), flags, src.handle, dst.handle,
+                                          s.ctypes.data_as(C.POINTER(C.c_double)) if want_ssim else None))
+        return s
+
+    def chain_async(self, f, src, dst, flags=NORM_CS_REFERENCE, ssim_dev=None):
+        self._ok(self.lib.norm_cuda_chain_async(self.h, self._raw(f), flags, src.handle, dst.handle,
+                                                C.c_void_p(ssim_dev) if ssim_dev else None))
+
+    def chain_host(self, f, host_in, host_out, frames, flags=NORM_CS_REFERENCE, want_ssim=True):
+        s = np.zeros(frames, np.float64) if want_ssim else None
+        self._ok(self.lib.norm_cuda_chain_host(self.h, self._raw(f), flags, host_in.ctypes.data, host_out.ctypes.data,
+                                               frames, s.ctypes.data_as(C.POINTER(C.c_double)) if want_ssim else None))
+        return s
+
+    def front(self, f, src, dst, flags=NORM_CS_REFERENCE):
+        self._ok(self.lib.norm_cuda_front(self.h, self._raw(f), flags, src.handle, dst.handle))
+
+    def blur(self, radius, src, dst): self._ok(self.lib.norm_cuda_blur(self.h, radius, src.handle, dst.handle))
+    def sobel(self, src, dst): self._ok(self.lib.norm_cuda_sobel(self.h, src.handle, dst.handle))
+    def sharpen(self, factor, src, dst): self._ok(self.lib.norm_cuda_sharpen(self.h, factor, src.handle, dst.handle))
+
+    def ssim(self, a, b):
+        s = np.zeros(a.frames, np.float64)
+        self._ok(self.lib.norm_cuda_ssim(self.h, a.handle, b.handle, s.ctypes.data_as(C.POINTER(C.c_double))))
+        return s
+
+    def ssim_moments(self, a, b):
+        m = np.zeros((a.frames, 5), np.float64)
+        self._ok(self.lib.norm_cuda_ssim_moments(self.h, a.handle, b.handle, m.ctypes.data_as(C.POINTER(C.c_double))))
+        return m
+
+
+class Texture:
+    """texture.rs:22-80: `from_image` = rgba8() + upload; here both happen on the GPU."""
+
+    def __init__(self, image):
+        self.image = image
+
+    @classmethod
+    def from_image(cls, ctx, img, mode=NORM_EXPAND_COMPAT):
+        w, h = img.dimensions()
+        dev = ctx.image_create(w, h, 1)
+        try:
+            ctx.expand_rgba8(img, mode, dev, 0)
+        except Exception:
+            dev.destroy()
+            raise
+        return cls(dev)
+
+    from_bytes = from_image  # texture.rs:18-20
+
+    def destroy(self): self.image.destroy()
+
+
+class EffectPipeline:
+    """effect_pipeline.rs: ordered (effect, predicate) list over ping-pong textures A / B.
+
+    `add_effect(label, shader, uniform, condition)`: `shader` names one of the reference's
+    compute shaders -- "gamma", "grayscale", "invert", "copy" -- instead of carrying WGSL.
+    `execute(feature_uniform)` runs each enabled effect as its own pass with the reference's
+    texture routing (#0: input->A, odd: A->B, even: B->A, effect_pipeline.rs:105-111);
+    `render` is the whole frame (execute + the fragment effect fs_main selects) in fused form.
+    """
+
+    def __init__(self, ctx, input_texture, texture_a, texture_b, effects, flags):
+        self.ctx, self.input, self._a, self._b, self.effects, self.flags = ctx, input_texture, texture_a, texture_b, effects, flags
+
+    @staticmethod
+    def builder(ctx, input_texture, width, height, flags=NORM_CS_REFERENCE):
+        return EffectPipelineBuilder(ctx, input_texture, width, height, flags)
+
+    def texture_a(self): return self._a
+
+    def update_effect_uniform(self, index, data):  # effect_pipeline.rs:53-62
+        if 0 <= index < len(self.effects):
+            self.effects[index]["uniform"] = data
+
+    def execute(self, feature_uniform):
+        w, h = self._a.image.width, self._a.image.height
+        for e in self.effects:
+            if not e["condition"](feature_uniform):
+                continue
+            f = FeatureUniform(w, h, 0)
+            flags = NORM_CS_RAW  # only the gamma pass reads the sRGB input texture
+            if e["shader"] == "gamma":
+                f.raw.gamma = int(e["uniform"] or 0)
+                flags = self.flags
+            elif e["shader"] == "grayscale":
+                f.raw.grayscale = 1
+            elif e["shader"] == "invert":
+                f.raw.invert = 1
+            self.ctx.front(f, e["src"].image, e["dst"].image, flags)
+
+    def render(self, feature_uniform, out=None):
+        out = out or self.ctx.image_create(self.input.image.width, self.input.image.height, self.input.image.frames)
+        self.ctx.effects(feature_uniform, self.input.image, out, self.flags)
+        return out
+
+
+class EffectPipelineBuilder:
+    SHADERS = ("gamma", "grayscale", "invert", "copy")
+
+    def __init__(self, ctx, input_texture, width, height, flags):
+        self.ctx, self.input, self.flags = ctx, input_texture, flags
+        self.a = Texture(ctx.image_create(width, height, 1))
+        self.b = Texture(ctx.image_create(width, height, 1))
+        self.effects = []
+
+    def add_effect(self, label, shader, uniform, condition):
+        if shader not in self.SHADERS:
+            raise NormError(_lib.NORM_E_UNSUPPORTED, f"unknown compute effect {shader!r}")
+        n = len(self.effects)
+        src, dst = (self.input, self.a) if n == 0 else ((self.a, self.b) if n % 2 == 1 else (self.b, self.a))
+        self.effects.append({"label": label, "shader": shader, "uniform": uniform, "condition": condition,
+                             "src": src, "dst": dst})
+        return self
+
+    def build(self):
+        return EffectPipeline(self.ctx, self.input, self.a, self.b, self.effects, self.flags)
+
+
+def reference_pipeline(ctx, input_texture, feature_uniform, flags=NORM_CS_REFERENCE):
+    """The wiring of AppState::new (app_state.rs:89-125)."""
+    w, h = input_texture.image.width, input_texture.image.height
+    return (EffectPipeline.builder(ctx, input_texture, w, h, flags)
+            .add_effect("gamma", "gamma", feature_uniform.gamma(), lambda f: True)
+            .add_effect("grayscale", "grayscale", None, lambda f: f.grayscale())
+            .add_effect("copy_after_grayscale", "copy", None, lambda f: f.grayscale())
+            .add_effect("invert", "invert", None, lambda f: f.invert())
+            .add_effect("copy_after_invert", "copy", None, lambda f: f.invert())
+            .build())
+
+
+# -- host-only helpers -------------------------------------------------------------------
+
+def blur_taps(radius):
+    taps, dmin = np.zeros(radius, np.float32), C.c_int32()
+    st = _lib.load().norm_blur_taps(radius, taps.ctypes.data_as(C.POINTER(C.c_float)), dmin)
+    if st != NORM_OK:
+        raise NormError(st, "blur radius outside 1..63")
+    return taps, dmin.value
+
+
+def front_lut(flags, gamma):
+    lut = np.zeros(256, np.uint8)
+    _lib.load().norm_front_lut(flags, gamma, lut.ctypes.data_as(C.POINTER(C.c_uint8)))
+    return lut
+
+
+def ssim_from_moments(m, npix):
+    m = np.ascontiguousarray(m, np.float64)
+    return float(_lib.load().norm_ssim_from_moments(m.ctypes.data_as(C.POINTER(C.c_double)), float(npix)))
+
+
+def plan_frames(frames, nranks, rank):
+    a, b = C.c_uint32(), C.c_uint32()
+    st = _lib.load().norm_plan_frames(frames, nranks, rank, a, b)
+    if st != NORM_OK:
+        raise NormError(st, "bad frame plan arguments")
+    return a.value, b.value
+
+
+def plan_band(f, height, nranks, rank):
+    r0, rows, up, down = C.c_uint32(), C.c_uint32(), C.c_uint32(), C.c_uint32()
+    st = _lib.load().norm_plan_band(Context._raw(f), height, nranks, rank, r0, rows, up, down)
+    if st != NORM_OK:
+        raise NormError(st, "bad band plan arguments")
+    return r0.value, rows.value, up.value, down.value

@@ -1,0 +1,975 @@
+// libnorm_cuda.so -- C ABI (include/norm_cuda.h) over the sm_100a kernels.
+// Host side of the CUDA backend: contexts, pitched RGBA8 image buffers, uploads, effect
+// dispatch (the EffectPipeline::execute analogue), SSIM, and the host-buffer pipeline.
+// No CPU fallback exists anywhere in this file: without a device every compute call fails.
+#include "../../include/norm_cuda.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "blur_kernels.cuh"
+#include "common.cuh"
+#include "stage_kernels.cuh"
+
+using namespace normk;
+
+// ---------------------------------------------------------------------------------------
+// objects
+// ---------------------------------------------------------------------------------------
+
+struct norm_img {
+    ImgView v;
+    bool owned;
+};
+
+namespace {
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+};
+
+// Everything one stream needs to run the chain: ping-pong temporaries, SSIM partials,
+// and (for the host-buffer pipeline) device staging for a chunk of frames.
+struct Slot {
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    DevBuf tmp[2];
+    DevBuf partials;
+    DevBuf stage_in, stage_out;
+};
+
+thread_local std::string g_create_error;
+
+}  // namespace
+
+struct norm_ctx {
+    int device = 0;
+    int sm_count = 0;
+    size_t total_mem = 0;
+    char name[128] = {0};
+    Slot main;
+    Slot pipe[3];
+    bool pipe_ready = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    uint64_t launches = 0;
+    DevBuf raw;         // expansion: packed scanlines
+    DevBuf results;     // per-frame moments (5) + ssim (1), doubles
+    double *h_results = nullptr;
+    size_t h_results_cap = 0;
+    bool smem_attr_set = false;
+};
+
+namespace {
+
+norm_status fail(norm_ctx *ctx, norm_status s, const std::string &msg) {
+    if (ctx) ctx->err = msg;
+    return s;
+}
+
+#define CU_TRY(ctx, expr)                                                                           \
+    do {                                                                                            \
+        cudaError_t e__ = (expr);                                                                   \
+        if (e__ != cudaSuccess) {                                                                   \
+            (void)cudaGetLastError();                                                               \
+            return fail(ctx, e__ == cudaErrorMemoryAllocation ? NORM_E_OOM : NORM_E_CUDA,           \
+                        std::string(#expr) + ": " + cudaGetErrorString(e__));                       \
+        }                                                                                           \
+    } while (0)
+
+#define NORM_TRY(expr)                     \
+    do {                                   \
+        norm_status s__ = (expr);          \
+        if (s__ != NORM_OK) return s__;    \
+    } while (0)
+
+norm_status ensure_buf(norm_ctx *ctx, DevBuf &b, size_t need) {
+    if (b.cap >= need) return NORM_OK;
+    if (b.p) {
+        // the buffer may still be in use by queued work
+        CU_TRY(ctx, cudaDeviceSynchronize());
+        CU_TRY(ctx, cudaFree(b.p));
+        b.p = nullptr;
+        b.cap = 0;
+    }
+    CU_TRY(ctx, cudaMalloc(&b.p, need));
+    b.cap = need;
+    return NORM_OK;
+}
+
+void free_buf(DevBuf &b) {
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr;
+    b.cap = 0;
+}
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+bool same_geometry(const ImgView &a, const ImgView &b) {
+    return a.w == b.w && a.h == b.h && a.frames == b.frames;
+}
+
+ImgView sub_frames(const ImgView &v, uint32_t frame0, uint32_t n) {
+    ImgView s = v;
+    s.ptr = v.ptr + (size_t)frame0 * v.frame_stride;
+    s.frames = n;
+    return s;
+}
+
+ImgView view_of(void *p, uint32_t w, uint32_t h, uint32_t frames) {
+    ImgView v;
+    v.ptr = static_cast<uint8_t *>(p);
+    v.pitch = align_up((size_t)w * 4, 256);
+    v.frame_stride = v.pitch * h;
+    v.w = w, v.h = h, v.frames = frames;
+    return v;
+}
+
+bool overlaps(const ImgView &a, const ImgView &b) {
+    const uint8_t *a0 = a.ptr, *a1 = a.ptr + (size_t)a.frames * a.frame_stride;
+    const uint8_t *b0 = b.ptr, *b1 = b.ptr + (size_t)b.frames * b.frame_stride;
+    return a0 < b1 && b0 < a1;
+}
+
+unsigned grid_for(const norm_ctx *ctx, size_t blocks_needed, int per_sm) {
+    const size_t cap = (size_t)ctx->sm_count * per_sm;
+    return (unsigned)std::max<size_t>(1, std::min(blocks_needed, cap));
+}
+
+#define LAUNCH_CHECK(ctx)                                                                  \
+    do {                                                                                   \
+        ++(ctx)->launches;                                                                 \
+        cudaError_t e__ = cudaGetLastError();                                              \
+        if (e__ != cudaSuccess)                                                            \
+            return fail(ctx, NORM_E_CUDA, std::string("kernel launch: ") + cudaGetErrorString(e__)); \
+    } while (0)
+
+// ---- host-side tables (plugin logic, not compute) -------------------------------------
+
+// image_shader.wgsl:83-103 under the floor convention: tap k has offset k - r/2, texel
+// delta floor(0.5 + offset), weight exp(-offset^2 / (2 sigma^2)), sigma = r/4; normalised.
+norm_status make_taps(uint32_t radius, Taps &t) {
+    if (radius < 1 || radius > NORM_MAX_BLUR_RADIUS) return NORM_E_INVALID_ARG;
+    const double r = (double)radius, sigma = r * 0.25;
+    double w[kMaxRadius + 1], sum = 0.0;
+    for (uint32_t k = 0; k < radius; ++k) {
+        const double off = -r / 2.0 + (double)k;
+        w[k] = std::exp(-(off * off) / (2.0 * sigma * sigma));
+        sum += w[k];
+    }
+    std::memset(&t, 0, sizeof(t));
+    for (uint32_t k = 0; k < radius; ++k) t.t[k] = (float)(w[k] / sum);
+    t.n = (int32_t)radius;
+    t.dmin = (int32_t)std::floor(0.5 - r / 2.0);
+    return NORM_OK;
+}
+
+double srgb_eotf(double c) { return c <= 0.04045 ? c / 12.92 : std::pow((c + 0.055) / 1.055, 2.4); }
+
+uint8_t unorm8(float v) {
+    if (!(v > 0.0f)) return 0;
+    if (v > 1.0f) v = 1.0f;
+    return (uint8_t)std::rint(v * 255.0f);
+}
+
+// texture.rs:36 (sRGB decode at load) + gamma_correct_compute.wgsl:25-40 + unorm8 store
+void make_lut(uint32_t flags, uint32_t gamma, Lut256 &lut, bool &identity) {
+    identity = true;
+    for (unsigned c = 0; c < 256; ++c) {
+        const double u = (double)c / 255.0;
+        float v = (float)((flags & NORM_CS_RAW) ? u : srgb_eotf(u));
+        if (gamma != 0u) {
+            const float gamma_value = (float)gamma / 100000.0f;
+            const float inv_gamma = 1.0f / gamma_value;
+            v = std::pow(v, inv_gamma);
+        }
+        lut.v[c] = unorm8(v);
+        identity = identity && lut.v[c] == c;
+    }
+}
+
+norm_status check_uniform(norm_ctx *ctx, const NormFeatureUniform *f, const ImgView &in) {
+    if (!f) return fail(ctx, NORM_E_INVALID_ARG, "feature uniform is NULL");
+    if (f->width != in.w || f->height != in.h)
+        return fail(ctx, NORM_E_DIM_MISMATCH, "FeatureUniform width/height differ from the image");
+    if (f->blur == 1 && (f->blur_radius < 1 || f->blur_radius > NORM_MAX_BLUR_RADIUS))
+        return fail(ctx, NORM_E_INVALID_ARG, "blur_radius outside 1..63");
+    return NORM_OK;
+}
+
+// ---- stage launchers -------------------------------------------------------------------
+
+norm_status launch_front(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const ImgView &out,
+                         const Lut256 &lut, bool use_lut, bool gray, bool inv) {
+    const size_t items = (size_t)((in.w + 3) / 4) * in.h * in.frames;
+    const unsigned grid = grid_for(ctx, (items + 255) / 256, 8);
+#define FRONT_CASE(L, G, I) \
+    if (use_lut == L && gray == G && inv == I) front_kernel<L, G, I><<<grid, 256, 0, s>>>(in, out, lut)
+    FRONT_CASE(false, false, false);
+    FRONT_CASE(false, false, true);
+    FRONT_CASE(false, true, false);
+    FRONT_CASE(false, true, true);
+    FRONT_CASE(true, false, false);
+    FRONT_CASE(true, false, true);
+    FRONT_CASE(true, true, false);
+    FRONT_CASE(true, true, true);
+#undef FRONT_CASE
+    LAUNCH_CHECK(ctx);
+    return NORM_OK;
+}
+
+template <int R>
+norm_status launch_blur_r(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const ImgView &out, const Taps &taps) {
+    const uint32_t tx = (in.w + kBlurTW - 1) / kBlurTW, ty = (in.h + kBlurTH - 1) / kBlurTH;
+    const size_t smem = blur_smem_bytes(taps.n);
+    CU_TRY(ctx, cudaFuncSetAttribute(blur_tile_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 1;
+    CU_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, blur_tile_kernel<R>, kBlurThreads, smem));
+    if (per_sm < 1) per_sm = 1;
+    const unsigned grid = grid_for(ctx, (size_t)tx * ty * in.frames, per_sm);
+    blur_tile_kernel<R><<<grid, kBlurThreads, smem, s>>>(in, out, taps, tx, ty);
+    LAUNCH_CHECK(ctx);
+    return NORM_OK;
+}
+
+norm_status launch_blur(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const ImgView &out, uint32_t radius) {
+    Taps taps;
+    if (make_taps(radius, taps) != NORM_OK) return fail(ctx, NORM_E_INVALID_ARG, "blur radius outside 1..63");
+    switch (radius) {
+    case 3: return launch_blur_r<3>(ctx, s, in, out, taps);
+    case 7: return launch_blur_r<7>(ctx, s, in, out, taps);
+    case 21: return launch_blur_r<21>(ctx, s, in, out, taps);
+    case 39: return launch_blur_r<39>(ctx, s, in, out, taps);
+    default: return launch_blur_r<0>(ctx, s, in, out, taps);
+    }
+}
+
+norm_status launch_sobel(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const ImgView &out) {
+    const uint32_t tx = (in.w + kStW - 1) / kStW, ty = (in.h + kStH - 1) / kStH;
+    const unsigned grid = grid_for(ctx, (size_t)tx * ty * in.frames, 8);
+    sobel_kernel<<<grid, 256, 0, s>>>(in, out, tx, ty);
+    LAUNCH_CHECK(ctx);
+    return NORM_OK;
+}
+
+norm_status launch_sharpen(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const ImgView &out, uint32_t factor) {
+    const uint32_t tx = (in.w + kStW - 1) / kStW, ty = (in.h + kStH - 1) / kStH;
+    const unsigned grid = grid_for(ctx, (size_t)tx * ty * in.frames, 8);
+    sharpen_kernel<<<grid, 256, 0, s>>>(in, out, (int)factor, tx, ty);
+    LAUNCH_CHECK(ctx);
+    return NORM_OK;
+}
+
+norm_status copy_view(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const ImgView &out) {
+    for (uint32_t f = 0; f < in.frames; ++f)
+        CU_TRY(ctx, cudaMemcpy2DAsync(out.ptr + (size_t)f * out.frame_stride, out.pitch,
+                                      in.ptr + (size_t)f * in.frame_stride, in.pitch, (size_t)in.w * 4, in.h,
+                                      cudaMemcpyDeviceToDevice, s));
+    return NORM_OK;
+}
+
+// SSIM of a[i] vs b[i]; d_moments / d_ssim are device arrays (5*frames / frames) or NULL.
+norm_status launch_ssim(norm_ctx *ctx, Slot &slot, const ImgView &a, const ImgView &b, double *d_moments,
+                        double *d_ssim) {
+    const size_t chunks = (size_t)((a.w + 3) / 4) * a.h;
+    size_t want = ((size_t)ctx->sm_count * 8 + a.frames - 1) / a.frames;  // ~8 CTAs per SM in total
+    const size_t max_useful = (chunks + 256 * 4 - 1) / (256 * 4);
+    uint32_t bpf = (uint32_t)std::max<size_t>(1, std::min(want, max_useful));
+    NORM_TRY(ensure_buf(ctx, slot.partials, (size_t)a.frames * bpf * 5 * sizeof(double)));
+    double *partials = static_cast<double *>(slot.partials.p);
+    // grid.y is limited to 65535: walk the batch in slices
+    for (uint32_t f0 = 0; f0 < a.frames; f0 += 65535u) {
+        const uint32_t n = std::min(65535u, a.frames - f0);
+        ssim_moments_kernel<<<dim3(bpf, n), 256, 0, slot.stream>>>(sub_frames(a, f0, n), sub_frames(b, f0, n),
+                                                                    partials + (size_t)f0 * bpf * 5);
+        LAUNCH_CHECK(ctx);
+    }
+    ssim_finalize_kernel<<<a.frames, 256, 0, slot.stream>>>(partials, bpf, (double)a.w * (double)a.h, d_moments,
+                                                             d_ssim);
+    LAUNCH_CHECK(ctx);
+    return NORM_OK;
+}
+
+struct StagePlan {
+    bool front = false, use_lut = false, gray = false, inv = false;
+    bool blur = false, sharpen = false, edge = false;
+    uint32_t radius = 0, factor = 0;
+    Lut256 lut;
+    int count() const { return (int)front + (int)blur + (int)sharpen + (int)edge; }
+};
+
+StagePlan make_plan(const NormFeatureUniform *f, uint32_t flags, bool chain) {
+    StagePlan p;
+    bool identity;
+    make_lut(flags, f->gamma, p.lut, identity);
+    p.use_lut = !identity;
+    p.gray = f->grayscale == 1;  // feature_uniform.rs:40-42: `== 1`
+    p.inv = f->invert == 1;
+    p.front = p.use_lut || p.gray || p.inv;
+    p.blur = f->blur == 1;
+    p.sharpen = f->sharpen == 1;
+    p.edge = f->edge_detect == 1;
+    p.radius = f->blur_radius;
+    p.factor = f->sharpen_factor;
+    if (!chain) {
+        // image_shader.wgsl:164-174: each effect overwrites `pixels` from texture A, so only
+        // the last enabled one in the order edge, sharpen, blur survives.
+        if (p.blur) p.sharpen = p.edge = false;
+        else if (p.sharpen) p.edge = false;
+    }
+    return p;
+}
+
+// Runs the planned stages in -> out on slot.stream using the slot's ping-pong temporaries,
+// `chunk` frames at a time so the temporaries stay small for large batches.
+norm_status run_stages_unfused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out) {
+    const int n = p.count();
+    if (n == 0) return copy_view(ctx, slot.stream, in, out);
+    const size_t frame_bytes = align_up((size_t)in.w * 4, 256) * in.h;
+    uint32_t chunk = in.frames;
+    if (n > 1) {
+        chunk = (uint32_t)std::max<size_t>(1, std::min<size_t>(in.frames, ((size_t)256 << 20) / frame_bytes));
+        NORM_TRY(ensure_buf(ctx, slot.tmp[0], frame_bytes * chunk));
+        if (n > 2) NORM_TRY(ensure_buf(ctx, slot.tmp[1], frame_bytes * chunk));
+    }
+    for (uint32_t f0 = 0; f0 < in.frames; f0 += chunk) {
+        const uint32_t nf = std::min(chunk, in.frames - f0);
+        ImgView cur = sub_frames(in, f0, nf);
+        const ImgView dst_final = sub_frames(out, f0, nf);
+        int done = 0, pp = 0;
+        auto next_dst = [&]() -> ImgView {
+            if (done == n - 1) return dst_final;
+            ImgView t = view_of(slot.tmp[pp].p, in.w, in.h, nf);
+            pp ^= 1;
+            return t;
+        };
+        if (p.front) {
+            ImgView d = next_dst();
+            NORM_TRY(launch_front(ctx, slot.stream, cur, d, p.lut, p.use_lut, p.gray, p.inv));
+            cur = d, ++done;
+        }
+        if (p.blur) {
+            ImgView d = next_dst();
+            NORM_TRY(launch_blur(ctx, slot.stream, cur, d, p.radius));
+            cur = d, ++done;
+        }
+        if (p.sharpen) {
+            ImgView d = next_dst();
+            NORM_TRY(launch_sharpen(ctx, slot.stream, cur, d, p.factor));
+            cur = d, ++done;
+        }
+        if (p.edge) {
+            ImgView d = next_dst();
+            NORM_TRY(launch_sobel(ctx, slot.stream, cur, d));
+            cur = d, ++done;
+        }
+    }
+    return NORM_OK;
+}
+
+// Fused single-pass chain kernels cover the hot configurations; everything else runs the
+// stage kernels back to back.  *fused tells the caller which happened.
+norm_status try_launch_chain_fused(norm_ctx *, cudaStream_t, const StagePlan &, const ImgView &, const ImgView &,
+                                   bool *fused) {
+    *fused = false;
+    return NORM_OK;
+}
+
+norm_status run_chain(norm_ctx *ctx, Slot &slot, const NormFeatureUniform *f, uint32_t flags, const ImgView &in,
+                      const ImgView &out, double *d_ssim) {
+    const StagePlan p = make_plan(f, flags, /*chain=*/true);
+    bool fused = false;
+    NORM_TRY(try_launch_chain_fused(ctx, slot.stream, p, in, out, &fused));
+    if (!fused) NORM_TRY(run_stages_unfused(ctx, slot, p, in, out));
+    if (d_ssim) NORM_TRY(launch_ssim(ctx, slot, out, in, nullptr, d_ssim));
+    return NORM_OK;
+}
+
+norm_status ensure_results(norm_ctx *ctx, uint32_t frames) {
+    const size_t need = (size_t)frames * 6 * sizeof(double);
+    NORM_TRY(ensure_buf(ctx, ctx->results, need));
+    if (ctx->h_results_cap < need) {
+        if (ctx->h_results) cudaFreeHost(ctx->h_results);
+        ctx->h_results = nullptr;
+        ctx->h_results_cap = 0;
+        CU_TRY(ctx, cudaMallocHost(&ctx->h_results, need));
+        ctx->h_results_cap = need;
+    }
+    return NORM_OK;
+}
+
+norm_status check_pair(norm_ctx *ctx, const norm_img *in, const norm_img *out, bool allow_alias) {
+    if (!ctx) return NORM_E_INVALID_ARG;
+    if (!in || !out) return fail(ctx, NORM_E_INVALID_ARG, "image handle is NULL");
+    if (!same_geometry(in->v, out->v)) return fail(ctx, NORM_E_DIM_MISMATCH, "images differ in width/height/frames");
+    if (!allow_alias && overlaps(in->v, out->v)) return fail(ctx, NORM_E_INVALID_ARG, "in and out may not alias");
+    return NORM_OK;
+}
+
+norm_status bind(norm_ctx *ctx) {
+    if (!ctx) return NORM_E_INVALID_ARG;
+    ctx->err.clear();
+    CU_TRY(ctx, cudaSetDevice(ctx->device));
+    return NORM_OK;
+}
+
+norm_status create_impl(int32_t device, void *ext_stream, bool use_ext, norm_ctx **out) {
+    if (!out) return NORM_E_INVALID_ARG;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        (void)cudaGetLastError();
+        g_create_error = std::string("no CUDA device available: ") + cudaGetErrorString(e) +
+                         " (libnorm_cuda has no CPU fallback)";
+        return NORM_E_CUDA;
+    }
+    if (device < 0 || device >= count) {
+        g_create_error = "device index out of range";
+        return NORM_E_INVALID_ARG;
+    }
+    norm_ctx *ctx = new (std::nothrow) norm_ctx();
+    if (!ctx) return NORM_E_OOM;
+    ctx->device = device;
+    auto bail = [&](cudaError_t ce, const char *what) {
+        g_create_error = std::string(what) + ": " + cudaGetErrorString(ce);
+        norm_cuda_destroy(ctx);
+        return NORM_E_CUDA;
+    };
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return bail(e, "cudaSetDevice");
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return bail(e, "cudaGetDeviceProperties");
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->total_mem = prop.totalGlobalMem;
+    std::snprintf(ctx->name, sizeof(ctx->name), "%s", prop.name);
+    if (prop.major < 10) {
+        g_create_error = std::string("device '") + prop.name + "' is sm_" + std::to_string(prop.major) +
+                         std::to_string(prop.minor) + "; libnorm_cuda is built for sm_100a only";
+        norm_cuda_destroy(ctx);
+        return NORM_E_UNSUPPORTED;
+    }
+    if (use_ext) {
+        ctx->main.stream = static_cast<cudaStream_t>(ext_stream);
+        ctx->main.own_stream = false;
+    } else {
+        if ((e = cudaStreamCreateWithFlags(&ctx->main.stream, cudaStreamNonBlocking)) != cudaSuccess)
+            return bail(e, "cudaStreamCreate");
+        ctx->main.own_stream = true;
+    }
+    if ((e = cudaEventCreate(&ctx->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaEventCreate(&ctx->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    *out = ctx;
+    return NORM_OK;
+}
+
+norm_status ensure_pipe(norm_ctx *ctx) {
+    if (ctx->pipe_ready) return NORM_OK;
+    for (auto &s : ctx->pipe) {
+        CU_TRY(ctx, cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        s.own_stream = true;
+    }
+    ctx->pipe_ready = true;
+    return NORM_OK;
+}
+
+void free_slot(Slot &s) {
+    free_buf(s.tmp[0]);
+    free_buf(s.tmp[1]);
+    free_buf(s.partials);
+    free_buf(s.stage_in);
+    free_buf(s.stage_out);
+    if (s.own_stream && s.stream) cudaStreamDestroy(s.stream);
+    s.stream = nullptr;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------
+
+extern "C" {
+
+int32_t norm_cuda_abi_version(void) { return NORM_CUDA_ABI_VERSION; }
+
+const char *norm_cuda_status_string(norm_status s) {
+    switch (s) {
+    case NORM_OK: return "ok";
+    case NORM_E_INVALID_ARG: return "invalid argument";
+    case NORM_E_UNSUPPORTED: return "unsupported input";
+    case NORM_E_CUDA: return "CUDA error";
+    case NORM_E_NCCL: return "NCCL error";
+    case NORM_E_OOM: return "out of memory";
+    case NORM_E_DIM_MISMATCH: return "dimension mismatch";
+    default: return "unknown status";
+    }
+}
+
+norm_status norm_cuda_create(int32_t device, norm_ctx **out) { return create_impl(device, nullptr, false, out); }
+
+norm_status norm_cuda_create_on_stream(int32_t device, void *cuda_stream, norm_ctx **out) {
+    return create_impl(device, cuda_stream, true, out);
+}
+
+void norm_cuda_destroy(norm_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    free_slot(ctx->main);
+    for (auto &s : ctx->pipe) free_slot(s);
+    free_buf(ctx->raw);
+    free_buf(ctx->results);
+    if (ctx->h_results) cudaFreeHost(ctx->h_results);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    (void)cudaGetLastError();
+    delete ctx;
+}
+
+const char *norm_cuda_last_error(const norm_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+norm_status norm_cuda_sync(norm_ctx *ctx) {
+    NORM_TRY(bind(ctx));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    if (ctx->pipe_ready)
+        for (auto &s : ctx->pipe) CU_TRY(ctx, cudaStreamSynchronize(s.stream));
+    return NORM_OK;
+}
+
+uint64_t norm_cuda_launch_count(const norm_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+norm_status norm_cuda_device_info(const norm_ctx *ctx, int32_t *sm_count, size_t *total_mem, char *name,
+                                  size_t name_cap) {
+    if (!ctx) return NORM_E_INVALID_ARG;
+    if (sm_count) *sm_count = ctx->sm_count;
+    if (total_mem) *total_mem = ctx->total_mem;
+    if (name && name_cap) std::snprintf(name, name_cap, "%s", ctx->name);
+    return NORM_OK;
+}
+
+norm_status norm_cuda_timer_start(norm_ctx *ctx) {
+    NORM_TRY(bind(ctx));
+    CU_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->main.stream));
+    return NORM_OK;
+}
+norm_status norm_cuda_timer_stop(norm_ctx *ctx) {
+    NORM_TRY(bind(ctx));
+    CU_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->main.stream));
+    return NORM_OK;
+}
+norm_status norm_cuda_timer_elapsed_ms(norm_ctx *ctx, float *ms) {
+    NORM_TRY(bind(ctx));
+    if (!ms) return fail(ctx, NORM_E_INVALID_ARG, "ms is NULL");
+    CU_TRY(ctx, cudaEventSynchronize(ctx->ev1));
+    CU_TRY(ctx, cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+    return NORM_OK;
+}
+
+// ---- images ----------------------------------------------------------------------------
+
+norm_status norm_cuda_image_create(norm_ctx *ctx, uint32_t width, uint32_t height, uint32_t frames, norm_img **out) {
+    NORM_TRY(bind(ctx));
+    if (!out) return fail(ctx, NORM_E_INVALID_ARG, "out is NULL");
+    *out = nullptr;
+    if (width == 0 || height == 0 || frames == 0) return fail(ctx, NORM_E_INVALID_ARG, "zero-sized image");
+    norm_img *img = new (std::nothrow) norm_img();
+    if (!img) return NORM_E_OOM;
+    img->v = view_of(nullptr, width, height, frames);
+    img->owned = true;
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, img->v.frame_stride * frames);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        delete img;
+        return fail(ctx, e == cudaErrorMemoryAllocation ? NORM_E_OOM : NORM_E_CUDA,
+                    std::string("cudaMalloc: ") + cudaGetErrorString(e));
+    }
+    img->v.ptr = static_cast<uint8_t *>(p);
+    *out = img;
+    return NORM_OK;
+}
+
+norm_status norm_cuda_image_wrap(norm_ctx *ctx, void *device_ptr, uint32_t width, uint32_t height, uint32_t frames,
+                                 size_t pitch, size_t frame_stride, norm_img **out) {
+    NORM_TRY(bind(ctx));
+    if (!out) return fail(ctx, NORM_E_INVALID_ARG, "out is NULL");
+    *out = nullptr;
+    if (!device_ptr || width == 0 || height == 0 || frames == 0) return fail(ctx, NORM_E_INVALID_ARG, "bad image");
+    if (pitch % 16 || frame_stride % 16 || (uintptr_t)device_ptr % 16 || pitch < (size_t)width * 4 ||
+        frame_stride < pitch * height)
+        return fail(ctx, NORM_E_INVALID_ARG, "pitch / frame_stride / pointer must be 16-byte aligned and large enough");
+    norm_img *img = new (std::nothrow) norm_img();
+    if (!img) return NORM_E_OOM;
+    img->v.ptr = static_cast<uint8_t *>(device_ptr);
+    img->v.pitch = pitch;
+    img->v.frame_stride = frame_stride;
+    img->v.w = width, img->v.h = height, img->v.frames = frames;
+    img->owned = false;
+    *out = img;
+    return NORM_OK;
+}
+
+void norm_cuda_image_destroy(norm_ctx *ctx, norm_img *img) {
+    if (!img) return;
+    if (img->owned && img->v.ptr) {
+        if (ctx) cudaSetDevice(ctx->device);
+        cudaFree(img->v.ptr);
+    }
+    delete img;
+}
+
+norm_status norm_cuda_image_info(const norm_img *img, uint32_t *width, uint32_t *height, uint32_t *frames,
+                                 size_t *pitch, size_t *frame_stride, void **device_ptr) {
+    if (!img) return NORM_E_INVALID_ARG;
+    if (width) *width = img->v.w;
+    if (height) *height = img->v.h;
+    if (frames) *frames = img->v.frames;
+    if (pitch) *pitch = img->v.pitch;
+    if (frame_stride) *frame_stride = img->v.frame_stride;
+    if (device_ptr) *device_ptr = img->v.ptr;
+    return NORM_OK;
+}
+
+static norm_status copy_frames(norm_ctx *ctx, cudaStream_t s, const ImgView &v, uint32_t frame0, uint32_t nframes,
+                               uint8_t *host, size_t host_pitch, bool to_device) {
+    if (frame0 + (uint64_t)nframes > v.frames) return fail(ctx, NORM_E_INVALID_ARG, "frame range outside image");
+    if (host_pitch == 0) host_pitch = (size_t)v.w * 4;
+    if (host_pitch < (size_t)v.w * 4) return fail(ctx, NORM_E_INVALID_ARG, "host_pitch < 4*width");
+    uint8_t *dev = v.ptr + (size_t)frame0 * v.frame_stride;
+    const bool one_shot = v.frame_stride == v.pitch * v.h;  // rows of consecutive frames are equidistant
+    const uint32_t groups = one_shot ? 1 : nframes;
+    const size_t rows = one_shot ? (size_t)v.h * nframes : v.h;
+    for (uint32_t g = 0; g < groups; ++g) {
+        uint8_t *d = dev + (size_t)g * v.frame_stride;
+        uint8_t *h = host + (size_t)g * host_pitch * v.h;
+        if (to_device)
+            CU_TRY(ctx, cudaMemcpy2DAsync(d, v.pitch, h, host_pitch, (size_t)v.w * 4, rows, cudaMemcpyHostToDevice, s));
+        else
+            CU_TRY(ctx, cudaMemcpy2DAsync(h, host_pitch, d, v.pitch, (size_t)v.w * 4, rows, cudaMemcpyDeviceToHost, s));
+    }
+    return NORM_OK;
+}
+
+norm_status norm_cuda_upload(norm_ctx *ctx, norm_img *img, uint32_t frame0, uint32_t nframes, const uint8_t *host,
+                             size_t host_pitch) {
+    NORM_TRY(bind(ctx));
+    if (!img || !host) return fail(ctx, NORM_E_INVALID_ARG, "NULL argument");
+    NORM_TRY(copy_frames(ctx, ctx->main.stream, img->v, frame0, nframes, const_cast<uint8_t *>(host), host_pitch, true));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    return NORM_OK;
+}
+
+norm_status norm_cuda_download(norm_ctx *ctx, const norm_img *img, uint32_t frame0, uint32_t nframes, uint8_t *host,
+                               size_t host_pitch) {
+    NORM_TRY(bind(ctx));
+    if (!img || !host) return fail(ctx, NORM_E_INVALID_ARG, "NULL argument");
+    NORM_TRY(copy_frames(ctx, ctx->main.stream, img->v, frame0, nframes, host, host_pitch, false));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    return NORM_OK;
+}
+
+norm_status norm_cuda_host_alloc(norm_ctx *ctx, size_t bytes, void **out) {
+    NORM_TRY(bind(ctx));
+    if (!out || bytes == 0) return fail(ctx, NORM_E_INVALID_ARG, "bad host_alloc request");
+    CU_TRY(ctx, cudaMallocHost(out, bytes));
+    return NORM_OK;
+}
+
+void norm_cuda_host_free(norm_ctx *ctx, void *p) {
+    if (!p) return;
+    if (ctx) cudaSetDevice(ctx->device);
+    cudaFreeHost(p);
+}
+
+// ---- expansion -------------------------------------------------------------------------
+
+static int channels_of(int ct) {
+    switch (ct) {
+    case 0: return 1;
+    case 2: return 3;
+    case 3: return 1;
+    case 4: return 2;
+    case 6: return 4;
+    default: return 0;
+    }
+}
+
+static bool valid_depth(int ct, int bd) {
+    switch (ct) {
+    case 0: return bd == 1 || bd == 2 || bd == 4 || bd == 8 || bd == 16;
+    case 3: return bd == 1 || bd == 2 || bd == 4 || bd == 8;
+    case 2:
+    case 4:
+    case 6: return bd == 8 || bd == 16;
+    default: return false;
+    }
+}
+
+static norm_status expand_to(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, const ImgView &out, uint32_t frame) {
+    if (!png || !png->pixels) return fail(ctx, NORM_E_INVALID_ARG, "png descriptor / pixels is NULL");
+    const int ct = png->color_type, bd = png->bit_depth;
+    if (!channels_of(ct) || !valid_depth(ct, bd)) return fail(ctx, NORM_E_INVALID_ARG, "invalid colour type / bit depth");
+    if (png->width != out.w || png->height != out.h) return fail(ctx, NORM_E_DIM_MISMATCH, "image size differs from png");
+    if (frame >= out.frames) return fail(ctx, NORM_E_INVALID_ARG, "frame out of range");
+    if (mode != NORM_EXPAND_COMPAT && mode != NORM_EXPAND_SPEC) return fail(ctx, NORM_E_INVALID_ARG, "unknown mode");
+    if (mode == NORM_EXPAND_COMPAT && (bd != 8 || ct == 3))
+        return fail(ctx, NORM_E_UNSUPPORTED,
+                    "compat mode mirrors Png::rgba8(): 8-bit grayscale / RGB / gray+alpha / RGBA only "
+                    "(grammar.rs:123-155)");
+    if (png->n_plte < 0 || png->n_plte > 256 || png->n_trns < 0 || png->n_trns > 256)
+        return fail(ctx, NORM_E_INVALID_ARG, "PLTE / tRNS too long");
+    if (ct == 3 && mode == NORM_EXPAND_SPEC && (!png->plte || png->n_plte == 0))
+        return fail(ctx, NORM_E_INVALID_ARG, "palette image without PLTE");
+    const size_t rowb = ((size_t)png->width * channels_of(ct) * bd + 7) / 8;
+    if (png->len < rowb * png->height) return fail(ctx, NORM_E_INVALID_ARG, "pixel buffer shorter than height*row_bytes");
+
+    NORM_TRY(ensure_buf(ctx, ctx->raw, align_up(rowb * png->height, 256)));
+    CU_TRY(ctx, cudaMemcpyAsync(ctx->raw.p, png->pixels, rowb * png->height, cudaMemcpyHostToDevice, ctx->main.stream));
+
+    ExpandParams p;
+    std::memset(&p, 0, sizeof(p));
+    p.src = static_cast<const uint8_t *>(ctx->raw.p);
+    p.src_row_bytes = rowb;
+    p.w = png->width, p.h = png->height;
+    p.bit_depth = bd, p.color_type = ct, p.mode = mode;
+    if (png->plte && png->n_plte > 0) {
+        std::memcpy(p.plte, png->plte, (size_t)png->n_plte * 3);
+        p.n_plte = png->n_plte;
+    }
+    if (png->trns && png->n_trns > 0) {
+        std::memcpy(p.trns, png->trns, (size_t)png->n_trns);
+        p.n_trns = png->n_trns;
+    }
+    if (ct != 3) p.n_trns = 0;  // per-index alpha only exists for palette images
+    const uint32_t smask = bd == 16 ? 0xFFFFu : ((1u << bd) - 1u);
+    if (mode == NORM_EXPAND_SPEC && png->trns) {
+        if (ct == 0 && png->n_trns >= 2) {
+            p.key[0] = (((uint32_t)png->trns[0] << 8) | png->trns[1]) & smask;
+            p.has_key = 1;
+        } else if (ct == 2 && png->n_trns >= 6) {
+            for (int c = 0; c < 3; ++c) p.key[c] = (((uint32_t)png->trns[2 * c] << 8) | png->trns[2 * c + 1]) & smask;
+            p.has_key = 1;
+        }
+    }
+    const size_t items = (size_t)((png->width + 3) / 4) * png->height;
+    const unsigned grid = grid_for(ctx, (items + 255) / 256, 8);
+    expand_kernel<<<grid, 256, 0, ctx->main.stream>>>(p, out, frame);
+    LAUNCH_CHECK(ctx);
+    return NORM_OK;
+}
+
+norm_status norm_cuda_expand_rgba8(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, norm_img *out, uint32_t frame) {
+    NORM_TRY(bind(ctx));
+    if (!out) return fail(ctx, NORM_E_INVALID_ARG, "out is NULL");
+    NORM_TRY(expand_to(ctx, png, mode, out->v, frame));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));  // png->pixels may be pageable: do not retain it
+    return NORM_OK;
+}
+
+norm_status norm_cuda_expand_rgba8_host(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, uint8_t *out_rgba8) {
+    NORM_TRY(bind(ctx));
+    if (!png || !out_rgba8) return fail(ctx, NORM_E_INVALID_ARG, "NULL argument");
+    if (png->width == 0 || png->height == 0) return fail(ctx, NORM_E_INVALID_ARG, "zero-sized image");
+    const size_t bytes = align_up((size_t)png->width * 4, 256) * png->height;
+    NORM_TRY(ensure_buf(ctx, ctx->main.tmp[0], bytes));
+    const ImgView v = view_of(ctx->main.tmp[0].p, png->width, png->height, 1);
+    NORM_TRY(expand_to(ctx, png, mode, v, 0));
+    NORM_TRY(copy_frames(ctx, ctx->main.stream, v, 0, 1, out_rgba8, 0, false));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    return NORM_OK;
+}
+
+// ---- effects ---------------------------------------------------------------------------
+
+norm_status norm_cuda_effects(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags, const norm_img *in,
+                              norm_img *out) {
+    NORM_TRY(bind(ctx));
+    NORM_TRY(check_pair(ctx, in, out, false));
+    NORM_TRY(check_uniform(ctx, f, in->v));
+    const StagePlan p = make_plan(f, flags, /*chain=*/false);
+    NORM_TRY(run_stages_unfused(ctx, ctx->main, p, in->v, out->v));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    return NORM_OK;
+}
+
+norm_status norm_cuda_chain_async(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags, const norm_img *in,
+                                  norm_img *out, double *ssim_dev) {
+    NORM_TRY(bind(ctx));
+    NORM_TRY(check_pair(ctx, in, out, false));
+    NORM_TRY(check_uniform(ctx, f, in->v));
+    return run_chain(ctx, ctx->main, f, flags, in->v, out->v, ssim_dev);
+}
+
+norm_status norm_cuda_chain(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags, const norm_img *in,
+                            norm_img *out, double *ssim) {
+    NORM_TRY(bind(ctx));
+    NORM_TRY(check_pair(ctx, in, out, false));
+    NORM_TRY(check_uniform(ctx, f, in->v));
+    double *d_ssim = nullptr;
+    if (ssim) {
+        NORM_TRY(ensure_results(ctx, in->v.frames));
+        d_ssim = static_cast<double *>(ctx->results.p);
+    }
+    NORM_TRY(run_chain(ctx, ctx->main, f, flags, in->v, out->v, d_ssim));
+    if (ssim)
+        CU_TRY(ctx, cudaMemcpyAsync(ctx->h_results, d_ssim, (size_t)in->v.frames * sizeof(double),
+                                    cudaMemcpyDeviceToHost, ctx->main.stream));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    if (ssim) std::memcpy(ssim, ctx->h_results, (size_t)in->v.frames * sizeof(double));
+    return NORM_OK;
+}
+
+norm_status norm_cuda_chain_host(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags, const uint8_t *in_rgba8,
+                                 uint8_t *out_rgba8, uint32_t frames, double *ssim) {
+    NORM_TRY(bind(ctx));
+    if (!f || !in_rgba8 || !out_rgba8 || frames == 0) return fail(ctx, NORM_E_INVALID_ARG, "NULL / empty argument");
+    if (f->width == 0 || f->height == 0) return fail(ctx, NORM_E_INVALID_ARG, "zero-sized frames");
+    const uint32_t w = f->width, h = f->height;
+    ImgView probe = view_of(nullptr, w, h, 1);
+    NORM_TRY(check_uniform(ctx, f, probe));
+    NORM_TRY(ensure_pipe(ctx));
+    NORM_TRY(ensure_results(ctx, frames));
+    double *d_ssim = ssim ? static_cast<double *>(ctx->results.p) : nullptr;
+
+    // chunk: ~64 MB of frames per stage buffer, at least 1 frame; three chunks in flight
+    const size_t frame_bytes = probe.frame_stride, host_frame = (size_t)w * 4 * h;
+    const uint32_t chunk = (uint32_t)std::max<size_t>(1, std::min<size_t>(frames, ((size_t)64 << 20) / frame_bytes));
+    for (auto &s : ctx->pipe) {
+        NORM_TRY(ensure_buf(ctx, s.stage_in, frame_bytes * chunk));
+        NORM_TRY(ensure_buf(ctx, s.stage_out, frame_bytes * chunk));
+    }
+    uint32_t ci = 0;
+    for (uint32_t f0 = 0; f0 < frames; f0 += chunk, ++ci) {
+        Slot &s = ctx->pipe[ci % 3];
+        const uint32_t nf = std::min(chunk, frames - f0);
+        const ImgView vin = view_of(s.stage_in.p, w, h, nf), vout = view_of(s.stage_out.p, w, h, nf);
+        NORM_TRY(copy_frames(ctx, s.stream, vin, 0, nf, const_cast<uint8_t *>(in_rgba8) + (size_t)f0 * host_frame, 0, true));
+        NORM_TRY(run_chain(ctx, s, f, flags, vin, vout, d_ssim ? d_ssim + f0 : nullptr));
+        NORM_TRY(copy_frames(ctx, s.stream, vout, 0, nf, out_rgba8 + (size_t)f0 * host_frame, 0, false));
+    }
+    for (auto &s : ctx->pipe) CU_TRY(ctx, cudaStreamSynchronize(s.stream));
+    if (ssim) {
+        CU_TRY(ctx, cudaMemcpyAsync(ctx->h_results, d_ssim, (size_t)frames * sizeof(double), cudaMemcpyDeviceToHost,
+                                    ctx->main.stream));
+        CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+        std::memcpy(ssim, ctx->h_results, (size_t)frames * sizeof(double));
+    }
+    return NORM_OK;
+}
+
+norm_status norm_cuda_front(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags, const norm_img *in,
+                            norm_img *out) {
+    NORM_TRY(bind(ctx));
+    NORM_TRY(check_pair(ctx, in, out, true));
+    NORM_TRY(check_uniform(ctx, f, in->v));
+    StagePlan p = make_plan(f, flags, true);
+    NORM_TRY(launch_front(ctx, ctx->main.stream, in->v, out->v, p.lut, p.use_lut, p.gray, p.inv));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    return NORM_OK;
+}
+
+norm_status norm_cuda_blur(norm_ctx *ctx, uint32_t radius, const norm_img *in, norm_img *out) {
+    NORM_TRY(bind(ctx));
+    NORM_TRY(check_pair(ctx, in, out, false));
+    NORM_TRY(launch_blur(ctx, ctx->main.stream, in->v, out->v, radius));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    return NORM_OK;
+}
+
+norm_status norm_cuda_sobel(norm_ctx *ctx, const norm_img *in, norm_img *out) {
+    NORM_TRY(bind(ctx));
+    NORM_TRY(check_pair(ctx, in, out, false));
+    NORM_TRY(launch_sobel(ctx, ctx->main.stream, in->v, out->v));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    return NORM_OK;
+}
+
+norm_status norm_cuda_sharpen(norm_ctx *ctx, uint32_t factor, const norm_img *in, norm_img *out) {
+    NORM_TRY(bind(ctx));
+    NORM_TRY(check_pair(ctx, in, out, false));
+    NORM_TRY(launch_sharpen(ctx, ctx->main.stream, in->v, out->v, factor));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    return NORM_OK;
+}
+
+// ---- SSIM ------------------------------------------------------------------------------
+
+static norm_status ssim_impl(norm_ctx *ctx, const norm_img *a, const norm_img *b, double *moments, double *ssim) {
+    NORM_TRY(bind(ctx));
+    NORM_TRY(check_pair(ctx, a, b, true));
+    const uint32_t n = a->v.frames;
+    NORM_TRY(ensure_results(ctx, n));
+    double *d_m = static_cast<double *>(ctx->results.p), *d_s = d_m + (size_t)n * 5;
+    NORM_TRY(launch_ssim(ctx, ctx->main, a->v, b->v, d_m, d_s));
+    CU_TRY(ctx, cudaMemcpyAsync(ctx->h_results, d_m, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost,
+                                ctx->main.stream));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    if (moments) std::memcpy(moments, ctx->h_results, (size_t)n * 5 * sizeof(double));
+    if (ssim) std::memcpy(ssim, ctx->h_results + (size_t)n * 5, (size_t)n * sizeof(double));
+    return NORM_OK;
+}
+
+norm_status norm_cuda_ssim(norm_ctx *ctx, const norm_img *a, const norm_img *b, double *ssim) {
+    if (ctx && !ssim) return fail(ctx, NORM_E_INVALID_ARG, "ssim is NULL");
+    return ssim_impl(ctx, a, b, nullptr, ssim);
+}
+
+norm_status norm_cuda_ssim_moments(norm_ctx *ctx, const norm_img *a, const norm_img *b, double *moments) {
+    if (ctx && !moments) return fail(ctx, NORM_E_INVALID_ARG, "moments is NULL");
+    return ssim_impl(ctx, a, b, moments, nullptr);
+}
+
+double norm_ssim_from_moments(const double moments[5], double npix) { return ssim_from_moments(moments, npix); }
+
+// ---- host-only helpers -----------------------------------------------------------------
+
+norm_status norm_blur_taps(uint32_t radius, float *taps, int32_t *dmin) {
+    Taps t;
+    if (!taps || !dmin || make_taps(radius, t) != NORM_OK) return NORM_E_INVALID_ARG;
+    std::memcpy(taps, t.t, radius * sizeof(float));
+    *dmin = t.dmin;
+    return NORM_OK;
+}
+
+norm_status norm_front_lut(uint32_t flags, uint32_t gamma, uint8_t lut[256]) {
+    if (!lut) return NORM_E_INVALID_ARG;
+    Lut256 l;
+    bool identity;
+    make_lut(flags, gamma, l, identity);
+    std::memcpy(lut, l.v, 256);
+    return NORM_OK;
+}
+
+norm_status norm_plan_frames(uint32_t frames, int32_t nranks, int32_t rank, uint32_t *frame0, uint32_t *nframes) {
+    if (nranks < 1 || rank < 0 || rank >= nranks || !frame0 || !nframes) return NORM_E_INVALID_ARG;
+    const uint32_t base = frames / (uint32_t)nranks, rem = frames % (uint32_t)nranks;
+    *frame0 = (uint32_t)rank * base + std::min<uint32_t>((uint32_t)rank, rem);
+    *nframes = base + ((uint32_t)rank < rem ? 1u : 0u);
+    return NORM_OK;
+}
+
+norm_status norm_plan_band(const NormFeatureUniform *f, uint32_t height, int32_t nranks, int32_t rank, uint32_t *row0,
+                           uint32_t *rows, uint32_t *halo_up, uint32_t *halo_down) {
+    if (!f || !row0 || !rows || !halo_up || !halo_down) return NORM_E_INVALID_ARG;
+    NORM_TRY(norm_plan_frames(height, nranks, rank, row0, rows));
+    // rows of SOURCE needed above / below an output row by the chained stencil stages
+    uint32_t up = 0, down = 0;
+    if (f->blur == 1) {
+        Taps t;
+        if (make_taps(f->blur_radius, t) != NORM_OK) return NORM_E_INVALID_ARG;
+        up += (uint32_t)(-t.dmin);
+        down += (uint32_t)(t.dmin + t.n - 1);
+    }
+    if (f->sharpen == 1) up += 1, down += 1;
+    if (f->edge_detect == 1) up += 1, down += 1;
+    *halo_up = std::min(up, *row0);
+    *halo_down = std::min(down, height - (*row0 + *rows));
+    return NORM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,376 @@
+"""GPU parity: every CUDA stage, called through the C ABI, against the CPU oracle on the same
+inputs.  Bars (BASELINE.json north_star): expansion bit-exact; filters bit-exact against
+the S-form oracle (hence within 1 LSB of the literal shader order, tests/test_oracle.py);
+SSIM within 1e-5 absolute (we hold 1e-9).
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+import norm_b200 as nb
+from conftest import GOLDEN, PNGSUITE, smooth_rgba, splitmix_rgba
+
+pytestmark = pytest.mark.gpu
+
+SSIM_TOL = 1e-5     # the stated tolerance
+SSIM_TIGHT = 1e-9   # what identical f32 lumas + f64 moments actually give
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = nb.Context(0)
+    yield c
+    c.close()
+
+
+def to_png(d):
+    return nb.Png(d.width, d.height, d.bit_depth, d.color_type, d.pixels, d.gamma, d.plte, d.trns)
+
+
+def read_png(oracle, path):
+    with open(path, "rb") as f:
+        return oracle.png_decode(f.read())
+
+
+VALID = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(PNGSUITE, "*.png"))
+               if not os.path.basename(p).startswith("x"))
+
+# odd sizes exercise ragged rows (w % 4 != 0), tiles smaller / larger than the CTA tile
+SIZES = [(1, 1), (3, 2), (5, 7), (33, 17), (64, 32), (65, 33), (130, 70), (257, 129), (200, 331)]
+
+
+def run_stage(ctx, fn, img, *args):
+    src = ctx.image_from_host(img)
+    dst = ctx.image_create(src.width, src.height, src.frames)
+    try:
+        fn(*args, src, dst)
+        return dst.download()
+    finally:
+        src.destroy(), dst.destroy()
+
+
+# ------------------------------------------------------------------ expansion (config 2)
+
+@pytest.mark.parametrize("name", VALID)
+def test_expand_spec_pngsuite(ctx, oracle, name):
+    d = read_png(oracle, os.path.join(PNGSUITE, name + ".png"))
+    got = to_png(d).rgba8(ctx, nb.NORM_EXPAND_SPEC)
+    assert np.array_equal(got, oracle.expand_rgba8(d, oracle.EXPAND_SPEC))
+
+
+def test_expand_compat_pngsuite(ctx, oracle):
+    n = 0
+    for name in VALID:
+        d = read_png(oracle, os.path.join(PNGSUITE, name + ".png"))
+        if d.bit_depth == 8 and d.color_type != 3:
+            got = to_png(d).rgba8(ctx, nb.NORM_EXPAND_COMPAT)
+            assert np.array_equal(got, oracle.expand_rgba8(d, oracle.EXPAND_COMPAT)), name
+            n += 1
+        else:
+            with pytest.raises(nb.NormError) as e:
+                to_png(d).rgba8(ctx, nb.NORM_EXPAND_COMPAT)
+            assert e.value.status == nb._lib.NORM_E_UNSUPPORTED
+    assert n >= 40
+
+
+def test_expand_synthetic_all_types(ctx, oracle):
+    """Every (colour type, depth) at ragged widths incl. tRNS keys and short palettes."""
+    rng = np.random.default_rng(7)
+    for ct, depths in ((0, (1, 2, 4, 8, 16)), (2, (8, 16)), (3, (1, 2, 4, 8)), (4, (8, 16)), (6, (8, 16))):
+        for bd in depths:
+            for (w, h) in ((1, 1), (7, 3), (37, 5), (130, 9)):
+                ch = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[ct]
+                rowb = (w * ch * bd + 7) // 8
+                pix = rng.integers(0, 256, size=rowb * h, dtype=np.uint8)
+                plte = trns = None
+                if ct == 3:
+                    n = min(1 << bd, 200)
+                    plte = rng.integers(0, 256, size=3 * n, dtype=np.uint8)
+                    trns = rng.integers(0, 256, size=n // 2, dtype=np.uint8)
+                elif ct == 0:
+                    trns = np.array([0, 1 if bd < 16 else 7], np.uint8)
+                elif ct == 2:
+                    trns = np.array([0, pix[0], 0, pix[min(1, pix.size - 1)], 0, pix[min(2, pix.size - 1)]], np.uint8)
+
+                class D:
+                    pass
+                d = D()
+                d.width, d.height, d.bit_depth, d.color_type, d.gamma = w, h, bd, ct, 0
+                d.compression = d.filter = d.interlace = 0
+                d.pixels, d.plte = pix, plte if plte is not None else np.zeros(0, np.uint8)
+                d.trns = trns if trns is not None else np.zeros(0, np.uint8)
+                od = oracle.DecodedPng.__new__(oracle.DecodedPng)
+                od.__dict__.update(d.__dict__)
+                exp = oracle.expand_rgba8(od, oracle.EXPAND_SPEC)
+                got = to_png(od).rgba8(ctx, nb.NORM_EXPAND_SPEC)
+                assert np.array_equal(got, exp), (ct, bd, w, h)
+
+
+def test_expand_errors(ctx):
+    pix = np.zeros(16, np.uint8)
+    with pytest.raises(nb.NormError):  # bad depth for RGB
+        nb.Png(2, 2, 4, 2, pix).rgba8(ctx, nb.NORM_EXPAND_SPEC)
+    with pytest.raises(nb.NormError):  # short buffer
+        nb.Png(4, 4, 8, 6, pix).rgba8(ctx, nb.NORM_EXPAND_SPEC)
+    with pytest.raises(nb.NormError):  # palette without PLTE
+        nb.Png(4, 4, 8, 3, pix).rgba8(ctx, nb.NORM_EXPAND_SPEC)
+
+
+# ------------------------------------------------------------------ single stages
+
+@pytest.mark.parametrize("gray,inv,gamma,cs", [(0, 0, 0, 0), (1, 0, 0, 0), (0, 1, 0, 1), (1, 1, 45455, 0),
+                                               (1, 0, 0, 1), (0, 0, 250000, 1), (1, 1, 100000, 1)])
+def test_front(ctx, oracle, gray, inv, gamma, cs):
+    for (w, h) in SIZES:
+        img = splitmix_rgba(w, h, seed=w * 131 + h)
+        f = nb.FeatureUniform(w, h, gamma)
+        f.raw.grayscale, f.raw.invert = gray, inv
+        got = run_stage(ctx, lambda s, d: ctx.front(f, s, d, cs), img)[0]
+        assert np.array_equal(got, oracle.front_s(img, cs, gamma, gray, inv)), (w, h)
+
+
+@pytest.mark.parametrize("radius", [1, 2, 3, 4, 5, 7, 9, 21, 39, 40, 63])
+def test_blur(ctx, oracle, radius):
+    sizes = SIZES if radius in (3, 21) else [(1, 1), (5, 7), (65, 33), (200, 131)]
+    for (w, h) in sizes:
+        img = smooth_rgba(w, h, seed=radius + w) if (w + h) % 2 else splitmix_rgba(w, h, seed=radius)
+        got = run_stage(ctx, lambda s, d: ctx.blur(radius, s, d), img)[0]
+        exp = oracle.blur_s(img, radius)
+        assert np.array_equal(got, exp), (radius, w, h, int(np.abs(got.astype(int) - exp).max()))
+
+
+def test_blur_bad_radius(ctx):
+    src = ctx.image_from_host(splitmix_rgba(8, 8))
+    dst = ctx.image_create(8, 8, 1)
+    for r in (0, 64, 1000):
+        with pytest.raises(nb.NormError) as e:
+            ctx.blur(r, src, dst)
+        assert e.value.status == nb._lib.NORM_E_INVALID_ARG
+    with pytest.raises(nb.NormError):  # aliasing
+        ctx.blur(3, src, src)
+    src.destroy(), dst.destroy()
+
+
+def test_sobel(ctx, oracle):
+    for (w, h) in SIZES:
+        for img in (splitmix_rgba(w, h, seed=5), smooth_rgba(w, h, seed=6)):
+            got = run_stage(ctx, ctx.sobel, img)[0]
+            assert np.array_equal(got, oracle.sobel_s(img)), (w, h)
+
+
+@pytest.mark.parametrize("factor", [1, 16, 40])
+def test_sharpen(ctx, oracle, factor):
+    for (w, h) in SIZES:
+        img = smooth_rgba(w, h, seed=factor)
+        got = run_stage(ctx, lambda s, d: ctx.sharpen(factor, s, d), img)[0]
+        assert np.array_equal(got, oracle.sharpen_s(img, factor)), (w, h)
+
+
+def test_ssim(ctx, oracle):
+    for (w, h) in SIZES[1:] + [(1024, 683)]:
+        a = smooth_rgba(w, h, seed=w)
+        b = oracle.blur_s(a, 7)
+        da, db = ctx.image_from_host(b), ctx.image_from_host(a)
+        got = ctx.ssim(da, db)[0]
+        exp = oracle.ssim(b, a)
+        assert abs(got - exp) <= SSIM_TIGHT and abs(got - exp) <= SSIM_TOL, (w, h, got, exp)
+        m = ctx.ssim_moments(da, db)[0]
+        assert np.allclose(m, oracle.ssim_moments(b, a), rtol=1e-13, atol=0)
+        assert abs(nb.ssim_from_moments(m, w * h) - exp) <= SSIM_TIGHT
+        assert abs(ctx.ssim(da, da)[0] - 1.0) <= 1e-12
+        da.destroy(), db.destroy()
+    # 1x1: N-1 = 0 -> NaN, as the reference's arithmetic gives (ssim.rs:169,180)
+    one = ctx.image_from_host(splitmix_rgba(1, 1))
+    assert np.isnan(ctx.ssim(one, one)[0])
+    # dimension mismatch (ssim.rs:92-95)
+    other = ctx.image_from_host(splitmix_rgba(2, 1))
+    with pytest.raises(nb.NormError) as e:
+        ctx.ssim(one, other)
+    assert e.value.status == nb._lib.NORM_E_DIM_MISMATCH
+    one.destroy(), other.destroy()
+
+
+def test_ssim_is_deterministic(ctx):
+    a, b = ctx.image_from_host(splitmix_rgba(640, 360, seed=1)), ctx.image_from_host(splitmix_rgba(640, 360, seed=2))
+    r = [ctx.ssim_moments(a, b).tobytes() for _ in range(3)]
+    assert r[0] == r[1] == r[2]
+    a.destroy(), b.destroy()
+
+
+# ------------------------------------------------------------------ pipelines
+
+def uniform(w, h, **kw):
+    f = nb.FeatureUniform(w, h, kw.pop("gamma", 0))
+    for k, v in kw.items():
+        setattr(f.raw, k, v)
+    return f
+
+
+def oracle_uniform(oracle, f):
+    r = f.raw
+    return oracle.make_uniform(r.width, r.height, r.gamma, r.grayscale, r.invert, r.blur, r.blur_radius, r.sharpen,
+                               r.sharpen_factor, r.edge_detect)
+
+
+@pytest.mark.parametrize("kw", [
+    dict(), dict(grayscale=1), dict(blur=1, blur_radius=7), dict(grayscale=1, blur=1, blur_radius=21),
+    dict(edge_detect=1), dict(sharpen=1), dict(blur=1, sharpen=1, edge_detect=1, blur_radius=3),
+    dict(sharpen=1, edge_detect=1, invert=1), dict(grayscale=2, blur=2, edge_detect=1, gamma=45455),
+])
+def test_effects_reference_semantics(ctx, oracle, kw):
+    """norm_cuda_effects == one reference frame: priority blur > sharpen > edge; flags are on iff == 1."""
+    for (w, h) in [(5, 7), (130, 70), (200, 131)]:
+        img = smooth_rgba(w, h, seed=11)
+        f = uniform(w, h, **kw)
+        for cs in (nb.NORM_CS_REFERENCE, nb.NORM_CS_RAW):
+            got = run_stage(ctx, lambda s, d: ctx.effects(f, s, d, cs), img)[0]
+            assert np.array_equal(got, oracle.effects(img, oracle_uniform(oracle, f), cs)), (kw, w, h, cs)
+
+
+CHAINS = [
+    dict(blur=1, blur_radius=21, edge_detect=1),                  # BASELINE config 4 chain
+    dict(grayscale=1, blur=1, blur_radius=21, edge_detect=1),     # config 3 chain
+    dict(grayscale=1, blur=1, blur_radius=21),                    # config 1 effect
+    dict(blur=1, blur_radius=3, edge_detect=1), dict(blur=1, blur_radius=7, edge_detect=1),
+    dict(blur=1, blur_radius=39, edge_detect=1), dict(blur=1, blur_radius=5, edge_detect=1),
+    dict(edge_detect=1), dict(blur=1, blur_radius=21), dict(), dict(invert=1, blur=1, sharpen=1, edge_detect=1, blur_radius=7),
+    dict(grayscale=1, gamma=45455, blur=1, blur_radius=9, edge_detect=1),
+]
+
+
+@pytest.mark.parametrize("kw", CHAINS)
+def test_chain(ctx, oracle, kw):
+    for (w, h) in [(1, 1), (5, 7), (64, 32), (130, 70), (333, 200)]:
+        frames = np.stack([smooth_rgba(w, h, seed=3), splitmix_rgba(w, h, seed=4, alpha=255),
+                           smooth_rgba(w, h, seed=5)[::-1].copy()])
+        f = uniform(w, h, **kw)
+        for cs in (nb.NORM_CS_RAW, nb.NORM_CS_REFERENCE):
+            src = ctx.image_from_host(frames)
+            dst = ctx.image_create(w, h, 3)
+            s = ctx.chain(f, src, dst, cs)
+            got = dst.download()
+            eo, es = oracle.chain_batch(frames, oracle_uniform(oracle, f), cs)
+            assert np.array_equal(got, eo), (kw, w, h, cs, int(np.abs(got.astype(int) - eo).max()))
+            if w * h > 1:
+                assert np.abs(s - es).max() <= SSIM_TIGHT, (kw, w, h, s, es)
+            src.destroy(), dst.destroy()
+
+
+def test_chain_host_pipeline(ctx, oracle):
+    """Host-buffer entry point (the e2e path): chunked upload / run / download."""
+    w, h, n = 160, 90, 7
+    frames = np.stack([smooth_rgba(w, h, seed=i) for i in range(n)])
+    f = uniform(w, h, blur=1, blur_radius=21, edge_detect=1)
+    out = np.empty_like(frames)
+    s = ctx.chain_host(f, frames, out, n, nb.NORM_CS_RAW)
+    eo, es = oracle.chain_batch(frames, oracle_uniform(oracle, f), oracle.CS_RAW)
+    assert np.array_equal(out, eo) and np.abs(s - es).max() <= SSIM_TIGHT
+    # pinned buffers
+    pin, ph = ctx.host_alloc(frames.nbytes)
+    pout, poh = ctx.host_alloc(frames.nbytes)
+    pin[:] = frames.reshape(-1)
+    s2 = ctx.chain_host(f, pin, pout, n, nb.NORM_CS_RAW)
+    assert np.array_equal(pout.reshape(frames.shape), eo) and np.array_equal(s, s2)
+    ctx.host_free(ph), ctx.host_free(poh)
+
+
+def test_uniform_validation(ctx):
+    src, dst = ctx.image_from_host(splitmix_rgba(16, 8)), ctx.image_create(16, 8, 1)
+    with pytest.raises(nb.NormError) as e:
+        ctx.chain(uniform(8, 8), src, dst)
+    assert e.value.status == nb._lib.NORM_E_DIM_MISMATCH
+    with pytest.raises(nb.NormError) as e:
+        ctx.chain(uniform(16, 8, blur=1, blur_radius=0), src, dst)
+    assert e.value.status == nb._lib.NORM_E_INVALID_ARG
+    bad = ctx.image_create(16, 9, 1)
+    with pytest.raises(nb.NormError):
+        ctx.effects(uniform(16, 8), src, bad)
+    src.destroy(), dst.destroy(), bad.destroy()
+
+
+# ------------------------------------------------------------------ BASELINE configs
+
+def test_config1_obama_luma_blur(ctx, oracle):
+    """configs[0]: tests/obama.png -> compat expansion (alpha 0) -> grayscale + blur r=21, sRGB texture."""
+    d = read_png(oracle, os.path.join(GOLDEN, "images", "obama.png"))
+    png = to_png(d)
+    tex = nb.Texture.from_image(ctx, png, nb.NORM_EXPAND_COMPAT)
+    rgba = tex.image.download()[0]
+    exp_rgba = oracle.expand_rgba8(d, oracle.EXPAND_COMPAT)
+    assert np.array_equal(rgba, exp_rgba) and (rgba[..., 3] == 0).all()
+    f = nb.FeatureUniform(png.width, png.height, png.gamma())
+    f.toggle_grayscale(), f.toggle_blur()
+    pipe = nb.reference_pipeline(ctx, tex, f)
+    out = pipe.render(f)
+    got = out.download()[0]
+    exp = oracle.effects(exp_rgba, oracle_uniform(oracle, f), oracle.CS_REFERENCE)
+    assert np.array_equal(got, exp)
+    # the staged EffectPipeline::execute leaves the same texture A the fused front stage computes
+    pipe.execute(f)
+    assert np.array_equal(pipe.texture_a().image.download()[0], oracle.front_s(exp_rgba, oracle.CS_REFERENCE, 0, 1, 0))
+    # literal shader loop order on a crop: within 1 LSB
+    crop = oracle.front_s(exp_rgba, oracle.CS_REFERENCE, 0, 1, 0)[200:328, 300:428].copy()
+    gc = run_stage(ctx, lambda s, d_: ctx.blur(21, s, d_), crop)[0]
+    assert np.abs(gc.astype(int) - oracle.blur_r(crop, 21).astype(int)).max() <= 1
+    # SSIM of the effect against the source, through the Png-level API
+    s = ctx.ssim(out, tex.image)[0]
+    assert abs(s - oracle.ssim(exp, exp_rgba)) <= SSIM_TIGHT
+    out.destroy(), tex.destroy()
+
+
+def test_config2_pngsuite_sobel(ctx, oracle):
+    """configs[1]: every valid PngSuite file: spec expansion -> Sobel line detection."""
+    for name in VALID:
+        d = read_png(oracle, os.path.join(PNGSUITE, name + ".png"))
+        tex = nb.Texture.from_image(ctx, to_png(d), nb.NORM_EXPAND_SPEC)
+        f = nb.FeatureUniform(d.width, d.height, d.gamma)
+        f.toggle_edge_detect()
+        out = ctx.image_create(d.width, d.height, 1)
+        ctx.effects(f, tex.image, out)
+        exp = oracle.effects(oracle.expand_rgba8(d, oracle.EXPAND_SPEC), oracle_uniform(oracle, f), oracle.CS_REFERENCE)
+        assert np.array_equal(out.download()[0], exp), name
+        out.destroy(), tex.destroy()
+
+
+def test_config3_8k_chain_properties(ctx, oracle):
+    """configs[2] at full size (7680x4320): oracle on sampled row bands + size-independent properties."""
+    w, h = 7680, 4320
+    img = splitmix_rgba(w, h, alpha=255)
+    yy = (np.arange(h, dtype=np.int64)[:, None] * 255 // (h - 1)).astype(np.uint8)
+    img[..., 0] = (img[..., 0].astype(np.uint16) + yy) // 2   # gradient so blur output is not flat
+    src, dst = ctx.image_from_host(img), ctx.image_create(w, h, 1)
+    f = uniform(w, h, grayscale=1, blur=1, blur_radius=21, edge_detect=1)
+    s = ctx.chain(f, src, dst, nb.NORM_CS_RAW)[0]
+    got = dst.download()[0]
+    # (1) bands incl. top and bottom edges vs the oracle run on the band + its stencil halo
+    for y0, y1 in ((0, 96), (2100, 2196), (h - 96, h)):
+        lo, hi = max(0, y0 - 12), min(h, y1 + 12)
+        band = np.ascontiguousarray(img[lo:hi])
+        eo, _ = oracle.chain(band, oracle.make_uniform(w, hi - lo, grayscale=1, blur=1, blur_radius=21, edge_detect=1), oracle.CS_RAW)
+        assert np.array_equal(got[y0:y1], eo[y0 - lo:y1 - lo]), (y0, y1)
+    # (2) output structure: gray, opaque
+    assert (got[..., 3] == 255).all() and np.array_equal(got[..., 0], got[..., 1]) and np.array_equal(got[..., 0], got[..., 2])
+    # (3) SSIM of the chain output vs source equals the oracle's SSIM on the GPU output
+    assert abs(s - oracle.ssim(got, img)) <= SSIM_TIGHT
+    # (4) idempotent front stage; SSIM(x,x) == 1
+    assert abs(ctx.ssim(src, src)[0] - 1.0) <= 1e-12
+    src.destroy(), dst.destroy()
+
+
+def test_config4_batch_frames_sample(ctx, oracle):
+    """configs[3] geometry (1920x1080 frames, blur r=21 + Sobel + SSIM) on a 6-frame sample;
+    frame results must not depend on batch position."""
+    w, h = 1920, 1080
+    frames = np.stack([splitmix_rgba(w, h, seed=0x6E6F726D ^ (i << 20), alpha=255) // 2 + smooth_rgba(w, h, seed=i) // 2
+                       for i in range(3)])
+    frames = np.concatenate([frames, frames[::-1]])
+    f = uniform(w, h, blur=1, blur_radius=21, edge_detect=1)
+    src, dst = ctx.image_from_host(frames), ctx.image_create(w, h, 6)
+    s = ctx.chain(f, src, dst, nb.NORM_CS_RAW)
+    got = dst.download()
+    eo, es = oracle.chain_batch(frames[:3], oracle_uniform(oracle, f), oracle.CS_RAW)
+    assert np.array_equal(got[:3], eo) and np.abs(s[:3] - es).max() <= SSIM_TIGHT
+    assert np.array_equal(got[3:], got[:3][::-1]) and np.array_equal(s[3:], s[:3][::-1])
+    src.destroy(), dst.destroy()
