@@ -6,12 +6,14 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
 #include <vector>
 
 #include "blur_kernels.cuh"
+#include "chain_kernels.cuh"
 #include "common.cuh"
 #include "stage_kernels.cuh"
 
@@ -62,7 +64,7 @@ struct norm_ctx {
     DevBuf results;     // per-frame moments (5) + ssim (1), doubles
     double *h_results = nullptr;
     size_t h_results_cap = 0;
-    bool smem_attr_set = false;
+    bool force_unfused = false;  // NORM_CUDA_FORCE_UNFUSED=1: run the chain as separate stage kernels
 };
 
 namespace {
@@ -372,20 +374,77 @@ norm_status run_stages_unfused(norm_ctx *ctx, Slot &slot, const StagePlan &p, co
     return NORM_OK;
 }
 
-// Fused single-pass chain kernels cover the hot configurations; everything else runs the
-// stage kernels back to back.  *fused tells the caller which happened.
-norm_status try_launch_chain_fused(norm_ctx *, cudaStream_t, const StagePlan &, const ImgView &, const ImgView &,
-                                   bool *fused) {
-    *fused = false;
+// Fused single-pass chain kernel (chain_kernels.cuh) covers front -> blur -> Sobel (+SSIM)
+// at the templated radii; every other combination runs the stage kernels back to back.
+template <int R, bool GRAY, bool FRONT>
+norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
+                         double *d_ssim) {
+    using C = FusedCfg<R, GRAY>;
+    auto kern = chain_fused_kernel<R, GRAY, FRONT>;
+    CU_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kSmem));
+    int per_sm = 1;
+    CU_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kFusedThreads, C::kSmem));
+    if (per_sm < 1) per_sm = 1;
+    FusedParams fp;
+    std::memset(&fp, 0, sizeof(fp));
+    fp.in = in, fp.out = out;
+    if (make_taps(R, fp.taps) != NORM_OK) return fail(ctx, NORM_E_INVALID_ARG, "bad radius");
+    fp.lut = p.lut;
+    fp.strips = (in.w + C::SW - 1) / C::SW;
+    // enough work items to fill the machine ~4 times over; bands no shorter than 64 rows
+    const size_t slots = (size_t)ctx->sm_count * per_sm;
+    const size_t base_items = (size_t)fp.strips * in.frames;
+    uint32_t bands = (uint32_t)std::min<size_t>(std::max<size_t>(1, (4 * slots + base_items - 1) / base_items),
+                                                std::max<uint32_t>(1, in.h / 64));
+    fp.band_rows = (in.h + bands - 1) / bands;
+    fp.bands = (in.h + fp.band_rows - 1) / fp.band_rows;
+    fp.invert = p.inv ? 1u : 0u;
+    fp.do_ssim = d_ssim ? 1u : 0u;
+    const uint32_t items_per_frame = fp.strips * fp.bands;
+    if (d_ssim) {
+        NORM_TRY(ensure_buf(ctx, slot.partials, (size_t)in.frames * items_per_frame * 5 * sizeof(double)));
+        fp.partials = static_cast<double *>(slot.partials.p);
+    }
+    const unsigned grid = grid_for(ctx, (size_t)items_per_frame * in.frames, per_sm);
+    kern<<<grid, kFusedThreads, C::kSmem, slot.stream>>>(fp);
+    LAUNCH_CHECK(ctx);
+    if (d_ssim) {
+        ssim_finalize_kernel<<<in.frames, 256, 0, slot.stream>>>(fp.partials, items_per_frame,
+                                                                 (double)in.w * (double)in.h, nullptr, d_ssim);
+        LAUNCH_CHECK(ctx);
+    }
     return NORM_OK;
+}
+
+template <int R>
+norm_status launch_fused_r(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
+                           double *d_ssim) {
+    if (p.gray) return launch_fused<R, true, true>(ctx, slot, p, in, out, d_ssim);
+    if (p.front) return launch_fused<R, false, true>(ctx, slot, p, in, out, d_ssim);
+    return launch_fused<R, false, false>(ctx, slot, p, in, out, d_ssim);
+}
+
+norm_status try_launch_chain_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in,
+                                   const ImgView &out, double *d_ssim, bool *fused) {
+    *fused = false;
+    if (!(p.blur && p.edge) || p.sharpen || ctx->force_unfused) return NORM_OK;
+    *fused = true;
+    switch (p.radius) {
+    case 3: return launch_fused_r<3>(ctx, slot, p, in, out, d_ssim);
+    case 7: return launch_fused_r<7>(ctx, slot, p, in, out, d_ssim);
+    case 21: return launch_fused_r<21>(ctx, slot, p, in, out, d_ssim);
+    case 39: return launch_fused_r<39>(ctx, slot, p, in, out, d_ssim);
+    default: *fused = false; return NORM_OK;
+    }
 }
 
 norm_status run_chain(norm_ctx *ctx, Slot &slot, const NormFeatureUniform *f, uint32_t flags, const ImgView &in,
                       const ImgView &out, double *d_ssim) {
     const StagePlan p = make_plan(f, flags, /*chain=*/true);
     bool fused = false;
-    NORM_TRY(try_launch_chain_fused(ctx, slot.stream, p, in, out, &fused));
-    if (!fused) NORM_TRY(run_stages_unfused(ctx, slot, p, in, out));
+    NORM_TRY(try_launch_chain_fused(ctx, slot, p, in, out, d_ssim, &fused));
+    if (fused) return NORM_OK;
+    NORM_TRY(run_stages_unfused(ctx, slot, p, in, out));
     if (d_ssim) NORM_TRY(launch_ssim(ctx, slot, out, in, nullptr, d_ssim));
     return NORM_OK;
 }
@@ -436,6 +495,7 @@ norm_status create_impl(int32_t device, void *ext_stream, bool use_ext, norm_ctx
     norm_ctx *ctx = new (std::nothrow) norm_ctx();
     if (!ctx) return NORM_E_OOM;
     ctx->device = device;
+    if (const char *e = std::getenv("NORM_CUDA_FORCE_UNFUSED")) ctx->force_unfused = e[0] == '1';
     auto bail = [&](cudaError_t ce, const char *what) {
         g_create_error = std::string(what) + ": " + cudaGetErrorString(ce);
         norm_cuda_destroy(ctx);

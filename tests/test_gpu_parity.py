@@ -374,3 +374,44 @@ def test_config4_batch_frames_sample(ctx, oracle):
     assert np.array_equal(got[:3], eo) and np.abs(s[:3] - es).max() <= SSIM_TIGHT
     assert np.array_equal(got[3:], got[:3][::-1]) and np.array_equal(s[3:], s[:3][::-1])
     src.destroy(), dst.destroy()
+
+
+def test_fused_sqrt_exhaustive_intensity_radicands(ctx, oracle):
+    """The fused kernel replaces sqrtf by the in-range Newton sequence: every possible intensity
+    radicand r^2+g^2+b^2 must still round exactly as sqrtf does.  4x4 constant blocks survive an
+    r=3 blur unchanged in their 2x2 interior, so every distinct radicand reaches the I pass."""
+    v = np.arange(256, dtype=np.int64)
+    r, g, b = np.meshgrid(v, v, v, indexing="ij")
+    keep = (r <= g) & (g <= b)
+    n = (r * r + g * g + b * b)[keep]
+    _, first = np.unique(n, return_index=True)
+    cols = np.stack([r[keep][first], g[keep][first], b[keep][first]], -1).astype(np.uint8)
+    nb_cols = cols.shape[0]
+    side = int(np.ceil(np.sqrt(nb_cols)))
+    grid = np.zeros((side * side, 4), np.uint8)
+    grid[:nb_cols, :3] = cols
+    grid[:, 3] = 255
+    img = np.repeat(np.repeat(grid.reshape(side, side, 4), 4, axis=0), 4, axis=1).copy()
+    h, w, _ = img.shape
+    f = uniform(w, h, blur=1, blur_radius=3, edge_detect=1)
+    src, dst = ctx.image_from_host(img), ctx.image_create(w, h, 1)
+    s = ctx.chain(f, src, dst, nb.NORM_CS_RAW)[0]
+    eo, es = oracle.chain(img, oracle_uniform(oracle, f), oracle.CS_RAW)
+    assert np.array_equal(dst.download()[0], eo) and abs(s - es) <= SSIM_TIGHT
+    src.destroy(), dst.destroy()
+
+
+def test_fused_matches_unfused_large_random(ctx, oracle):
+    """Dense random Sobel inputs: fused kernel vs the stage kernels (which use sqrtf) vs oracle."""
+    w, h = 1531, 1187
+    img = splitmix_rgba(w, h, seed=99)
+    f = uniform(w, h, blur=1, blur_radius=7, edge_detect=1)
+    src, dst = ctx.image_from_host(img), ctx.image_create(w, h, 1)
+    ctx.chain(f, src, dst, nb.NORM_CS_RAW)
+    fused = dst.download()[0]
+    tmp = ctx.image_create(w, h, 1)
+    ctx.blur(7, src, tmp)
+    ctx.sobel(tmp, dst)
+    assert np.array_equal(fused, dst.download()[0])
+    assert np.array_equal(fused, oracle.sobel_s(oracle.blur_s(img, 7)))
+    src.destroy(), dst.destroy(), tmp.destroy()
