@@ -390,6 +390,8 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
     fp.in = in, fp.out = out;
     if (make_taps(R, fp.taps) != NORM_OK) return fail(ctx, NORM_E_INVALID_ARG, "bad radius");
     fp.lut = p.lut;
+    for (int k = 0; k <= R; ++k)
+        fp.tp[k] = make_float2(k < R ? fp.taps.t[k] : 0.0f, k >= 1 ? fp.taps.t[k - 1] : 0.0f);
     fp.strips = (in.w + C::SW - 1) / C::SW;
     // enough work items to fill the machine ~4 times over; bands no shorter than 64 rows
     const size_t slots = (size_t)ctx->sm_count * per_sm;
