@@ -224,6 +224,36 @@ norm_status norm_cuda_ssim_moments(norm_ctx *ctx, const norm_img *a, const norm_
 /* Host-only: SSIM from (all-reduced) moments over npix pixels (ssim.rs:127-183 in f64). */
 double norm_ssim_from_moments(const double moments[5], double npix);
 
+/* Has no counterpart in the reference.  SSIM for callers that are not allowed to allocate device
+ * memory: a render / processing loop that must stay clear of the device allocator while frames
+ * are in flight (cudaMalloc and cudaFree stall the whole GPU), or a host that has given all
+ * device memory to its own pool so that a cudaMalloc from this library would fail.
+ * Same result as norm_cuda_ssim / norm_cuda_ssim_moments, but the partial sums go to a fixed
+ * 160 KiB array built into the library (resident on every GPU that loads it, until exit) and
+ * the call creates nothing: no context, no cudaMalloc/cudaFree, no pinned memory.
+ *   a_dev, b_dev   device pointers to `frames` pitched RGBA8 frames (same geometry for both;
+ *                  pitch % 16 == 0, frame_stride % 16 == 0, 16-byte aligned), e.g. from
+ *                  norm_cuda_image_info or the caller's own pool;
+ *   ssim_dev       device array of `frames` doubles, or NULL;
+ *   moments_dev    device array of 5*frames doubles, or NULL (at least one of the two);
+ *   cuda_stream    cudaStream_t cast to void* (NULL = default stream); the work is queued on
+ *                  it and the call returns without waiting.
+ * Limits and rules:
+ *   - frames <= NORM_SSIM_STATIC_MAX_FRAMES per call, otherwise NORM_E_INVALID_ARG with a message
+ *     saying so (split the batch); any width / height.
+ *   - The device that is current when you call is the one used.  The first call on each device
+ *     looks up the array's address (cudaGetSymbolAddress); make that first call outside any
+ *     stream capture.
+ *   - All calls on a device share the one array.  Two calls whose GPU work can overlap (different
+ *     streams, different threads) corrupt each other's sums: keep them on one stream or order
+ *     them yourself.  Nothing carries over between calls - each launch overwrites the slots it
+ *     reads - so there is nothing to reset.
+ *   - Error text: norm_cuda_last_error(NULL) on the calling thread. */
+#define NORM_SSIM_STATIC_MAX_FRAMES 1024u
+norm_status norm_cuda_ssim_static(const void *a_dev, const void *b_dev, uint32_t width, uint32_t height,
+                                  uint32_t frames, size_t pitch, size_t frame_stride, double *ssim_dev,
+                                  double *moments_dev, void *cuda_stream);
+
 /* ---- host-only planning helpers (usable without a GPU) ------------------------------ */
 
 /* Normalised 1-D taps of the separable blur and the texel offset of tap 0

@@ -80,6 +80,7 @@ PROTOTYPES = {
     "norm_cuda_ssim": (_i32, [_vp, _vp, _vp, _dp]),
     "norm_cuda_ssim_moments": (_i32, [_vp, _vp, _vp, _dp]),
     "norm_ssim_from_moments": (C.c_double, [_dp, C.c_double]),
+    "norm_cuda_ssim_static": (_i32, [_vp, _vp, _u32, _u32, _u32, _sz, _sz, _vp, _vp, _vp]),
     "norm_blur_taps": (_i32, [_u32, C.POINTER(C.c_float), C.POINTER(_i32)]),
     "norm_front_lut": (_i32, [_u32, _u32, C.POINTER(C.c_uint8)]),
     "norm_plan_band": (_i32, [_fu, _u32, _i32, _i32, C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_u32),

@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -987,6 +988,95 @@ norm_status norm_cuda_ssim_moments(norm_ctx *ctx, const norm_img *a, const norm_
 }
 
 double norm_ssim_from_moments(const double moments[5], double npix) { return ssim_from_moments(moments, npix); }
+
+// ---- SSIM for callers that may not allocate ----------------------------------------------
+//
+// norm_cuda_ssim needs scratch for its per-CTA partial sums and takes it from a context, which
+// gets it from cudaMalloc.  Two kinds of caller cannot live with that: a frame loop that must
+// never touch the device allocator once it is running (cudaMalloc/cudaFree synchronise the
+// whole device and would stall every frame in flight), and a host application that has already
+// handed all device memory to its own pool, where a library-side cudaMalloc simply fails.
+// For them the partial sums live in this fixed array inside the library image.  Every GPU that
+// loads the library carries these 160 KiB until the process exits.
+//
+// `g_ssim_static_scratch` below is, for host code, only a handle: its host-side address is not
+// a device address.  The device address is looked up once per device with
+// cudaGetSymbolAddress (that device being current) and that pointer is what the kernels get.
+#define NORM_SSIM_STATIC_SLOTS 4096  /* partial-sum slots of 5 doubles */
+static __device__ __align__(256) double g_ssim_static_scratch[NORM_SSIM_STATIC_SLOTS * 5];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+double *g_static_scratch_dev[kMaxDevices] = {nullptr};
+
+norm_status static_fail(norm_status s, const std::string &msg) {
+    g_create_error = msg;
+    return s;
+}
+}  // namespace
+
+norm_status norm_cuda_ssim_static(const void *a_dev, const void *b_dev, uint32_t width, uint32_t height,
+                                  uint32_t frames, size_t pitch, size_t frame_stride, double *ssim_dev,
+                                  double *moments_dev, void *cuda_stream) {
+    if (!a_dev || !b_dev || (!ssim_dev && !moments_dev))
+        return static_fail(NORM_E_INVALID_ARG, "norm_cuda_ssim_static: NULL image or no output pointer");
+    if (width == 0 || height == 0 || frames == 0)
+        return static_fail(NORM_E_INVALID_ARG, "norm_cuda_ssim_static: zero-sized input");
+    if (frames > NORM_SSIM_STATIC_MAX_FRAMES)
+        return static_fail(NORM_E_INVALID_ARG,
+                           "norm_cuda_ssim_static: " + std::to_string(frames) + " frames exceed the fixed scratch; at most " +
+                                   std::to_string(NORM_SSIM_STATIC_MAX_FRAMES) +
+                                   " frames per call (split the batch, or use norm_cuda_ssim which allocates)");
+    if (pitch % 16 || frame_stride % 16 || (uintptr_t)a_dev % 16 || (uintptr_t)b_dev % 16 ||
+        pitch < (size_t)width * 4 || frame_stride < pitch * height)
+        return static_fail(NORM_E_INVALID_ARG, "norm_cuda_ssim_static: pitch / frame_stride / pointers must be 16-byte aligned and large enough");
+
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+        (void)cudaGetLastError();
+        return static_fail(NORM_E_CUDA, std::string("norm_cuda_ssim_static: cudaGetDevice: ") + cudaGetErrorString(e));
+    }
+    double *scratch = nullptr;
+    {
+        // one-time set-up for this device: resolve the array's device address
+        std::lock_guard<std::mutex> lock(g_static_mu);
+        if (!g_static_scratch_dev[dev]) {
+            double *ptr = nullptr;
+            e = cudaGetSymbolAddress(reinterpret_cast<void **>(&ptr), g_ssim_static_scratch);
+            if (e != cudaSuccess || !ptr) {
+                (void)cudaGetLastError();
+                return static_fail(NORM_E_CUDA, std::string("norm_cuda_ssim_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+            }
+            g_static_scratch_dev[dev] = ptr;
+        }
+        scratch = g_static_scratch_dev[dev];
+    }
+
+    ImgView a, b;
+    a.ptr = static_cast<uint8_t *>(const_cast<void *>(a_dev));
+    a.pitch = pitch, a.frame_stride = frame_stride, a.w = width, a.h = height, a.frames = frames;
+    b = a;
+    b.ptr = static_cast<uint8_t *>(const_cast<void *>(b_dev));
+
+    // partial-sum slots per frame: enough CTAs to fill the GPU, never more than the array holds.
+    // Every slot a launch reads is written by that same launch first, so nothing has to be cleared.
+    const size_t chunks = (size_t)((width + 3) / 4) * height;
+    const size_t max_useful = (chunks + 256 * 4 - 1) / (256 * 4);
+    size_t want = (size_t)NORM_SSIM_STATIC_SLOTS / frames;
+    want = std::min(want, max_useful);
+    want = std::min(want, ((size_t)1184 + frames - 1) / frames);
+    const uint32_t bpf = (uint32_t)std::max<size_t>(1, want);
+    cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
+    ssim_moments_kernel<<<dim3(bpf, frames), 256, 0, s>>>(a, b, scratch);
+    if ((e = cudaGetLastError()) != cudaSuccess)
+        return static_fail(NORM_E_CUDA, std::string("norm_cuda_ssim_static: launch: ") + cudaGetErrorString(e));
+    ssim_finalize_kernel<<<frames, 256, 0, s>>>(scratch, bpf, (double)width * (double)height, moments_dev, ssim_dev);
+    if ((e = cudaGetLastError()) != cudaSuccess)
+        return static_fail(NORM_E_CUDA, std::string("norm_cuda_ssim_static: launch: ") + cudaGetErrorString(e));
+    return NORM_OK;
+}
 
 // ---- host-only helpers -----------------------------------------------------------------
 
