@@ -30,7 +30,7 @@ def _stale(target, sources):
 
 
 def build_cuda(force=False, verbose=False):
-    srcs = [os.path.join(CSRC, n) for n in sorted(os.listdir(CSRC))]
+    srcs = [os.path.join(CSRC, n) for n in sorted(os.listdir(CSRC)) if n != "norm_nccl.cu"]
     srcs += [os.path.join(ROOT, "include", "norm_cuda.h"), os.path.abspath(__file__)]
     if not (force or _stale(LIB, srcs)):
         return LIB
@@ -50,6 +50,28 @@ def build_cuda(force=False, verbose=False):
     return LIB
 
 
+NCCL_LIB = os.path.join(ROOT, "norm_b200", "libnorm_nccl.so")
+
+
+def build_nccl(force=False):
+    """libnorm_nccl.so: the SSIM-moments all-reduce, linked against the system NCCL (libnccl.so.2;
+    inside a torch process the already-loaded bundled NCCL with the same SONAME is reused)."""
+    src = os.path.join(CSRC, "norm_nccl.cu")
+    deps = [src, os.path.join(ROOT, "include", "norm_nccl.h"), os.path.abspath(__file__)]
+    if not (force or _stale(NCCL_LIB, deps)):
+        return NCCL_LIB
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    env = dict(os.environ)
+    env.pop("CC", None), env.pop("CXX", None)
+    cmd = [nvcc, "-ccbin", "/usr/bin/g++", "-gencode", "arch=compute_100a,code=sm_100a", "-O2", "-std=c++17",
+           "-Xcompiler", "-fPIC", "-shared", "-cudart", "static", "-o", NCCL_LIB, src, "-lnccl"]
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout + r.stderr)
+        raise RuntimeError("nvcc failed for norm_nccl.cu")
+    return NCCL_LIB
+
+
 def build_oracle(force=False):
     args = ["make", "-C", os.path.join(ROOT, "oracle"), "-s"]
     if force:
@@ -61,4 +83,5 @@ def build_oracle(force=False):
 if __name__ == "__main__":
     force = "--force" in sys.argv
     print(build_cuda(force=force, verbose="-v" in sys.argv))
+    print(build_nccl(force=force))
     print(build_oracle(force=force))

@@ -199,6 +199,34 @@ norm_status norm_cuda_chain_host(norm_ctx *ctx, const NormFeatureUniform *f, uin
                                  const uint8_t *in_rgba8, uint8_t *out_rgba8, uint32_t frames,
                                  double *ssim);
 
+/* ---- one giant image, row-band sharded over several GPUs ------------------ */
+
+/* The chain on one rank's band.  `in` / `out` hold the band plus its stencil halo rows
+ * (norm_plan_band: halo_up + rows + halo_down rows of the full image, full width) and
+ * FeatureUniform.height is that extended height.  Output rows of the halo are scratch; rows
+ * [own_row0, own_row0 + own_rows) are exact (a halo row only ever feeds halo outputs, and
+ * ClampToEdge applies at the true image edge because bands at the edge have no halo there).
+ * moments (host, 5 doubles per frame, may be NULL): the SSIM moments of the OWNED rows only,
+ * to be summed over ranks (ncclAllReduce, norm_nccl.h) and finished with
+ * norm_ssim_from_moments(sum, width * full_height).  Stands where Png::compute_sim's passes
+ * over the whole image do (src/png/ssim.rs:18-183). */
+norm_status norm_cuda_chain_band(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags,
+                                 const norm_img *in, norm_img *out, uint32_t own_row0, uint32_t own_rows,
+                                 double *moments);
+
+/* Peer access between the one-process-per-GPU ranks: export an owned image as a 64-byte CUDA
+ * IPC handle, open a neighbour's handle as a device pointer valid in this process (peer access
+ * over NVLink is enabled on open), close it when done.  No reference counterpart (the
+ * reference is single-device). */
+norm_status norm_cuda_ipc_export(norm_ctx *ctx, const norm_img *img, uint8_t handle[64]);
+norm_status norm_cuda_ipc_open(norm_ctx *ctx, const uint8_t handle[64], void **device_ptr);
+norm_status norm_cuda_ipc_close(norm_ctx *ctx, void *device_ptr);
+/* Halo exchange: copies `nrows` rows starting at src_row of a (local or peer-mapped) RGBA8
+ * buffer with pitch src_pitch into rows [dst_row, dst_row+nrows) of frame 0 of `dst`, on the
+ * context's stream (asynchronous; order with norm_cuda_sync). */
+norm_status norm_cuda_copy_rows(norm_ctx *ctx, norm_img *dst, uint32_t dst_row, const void *src_device_ptr,
+                                size_t src_pitch, uint32_t src_row, uint32_t nrows);
+
 /* Single stages, for callers that compose their own pipeline (EffectPipelineBuilder::
  * add_effect, effect_pipeline.rs:92-123) and for per-stage parity tests. */
 /* gamma_correct_compute.wgsl:15-42 + grayscale_compute.wgsl:11-29 + invert_compute.wgsl:11-33 */

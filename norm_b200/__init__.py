@@ -9,4 +9,6 @@ from ._lib import (LIB_PATH, NORM_CS_RAW, NORM_CS_REFERENCE, NORM_EXPAND_COMPAT,
 from .api import (Context, DeviceImage, EffectPipeline, EffectPipelineBuilder, FeatureUniform, NormError, Png,
                   Texture, blur_taps, front_lut, plan_band, plan_frames, reference_pipeline, ssim_from_moments)
 
+from . import sharding  # noqa: E402,F401
+
 __all__ = [n for n in dir() if not n.startswith("_")]

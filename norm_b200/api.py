@@ -258,6 +258,29 @@ class Context:
                                                frames, s.ctypes.data_as(C.POINTER(C.c_double)) if want_ssim else None))
         return s
 
+    def chain_band(self, f, src, dst, own_row0, own_rows, flags=NORM_CS_REFERENCE, want_moments=True):
+        """Chain on band + halo; returns the SSIM moments of the owned rows (frames x 5)."""
+        m = np.zeros((src.frames, 5), np.float64) if want_moments else None
+        self._ok(self.lib.norm_cuda_chain_band(self.h, self._raw(f), flags, src.handle, dst.handle, own_row0, own_rows,
+                                               m.ctypes.data_as(C.POINTER(C.c_double)) if want_moments else None))
+        return m
+
+    def ipc_export(self, img):
+        h = (C.c_uint8 * 64)()
+        self._ok(self.lib.norm_cuda_ipc_export(self.h, img.handle, h))
+        return bytes(h)
+
+    def ipc_open(self, handle):
+        p = C.c_void_p()
+        buf = (C.c_uint8 * 64).from_buffer_copy(handle)
+        self._ok(self.lib.norm_cuda_ipc_open(self.h, buf, C.byref(p)))
+        return p.value
+
+    def ipc_close(self, ptr): self._ok(self.lib.norm_cuda_ipc_close(self.h, C.c_void_p(ptr)))
+
+    def copy_rows(self, dst, dst_row, src_ptr, src_pitch, src_row, nrows):
+        self._ok(self.lib.norm_cuda_copy_rows(self.h, dst.handle, dst_row, C.c_void_p(src_ptr), src_pitch, src_row, nrows))
+
     def front(self, f, src, dst, flags=NORM_CS_REFERENCE):
         self._ok(self.lib.norm_cuda_front(self.h, self._raw(f), flags, src.handle, dst.handle))
 

@@ -379,7 +379,7 @@ norm_status run_stages_unfused(norm_ctx *ctx, Slot &slot, const StagePlan &p, co
 // at the templated radii; every other combination runs the stage kernels back to back.
 template <int R, bool GRAY, bool FRONT>
 norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
-                         double *d_ssim) {
+                         double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1) {
     using C = FusedCfg<R, GRAY>;
     auto kern = chain_fused_kernel<R, GRAY, FRONT>;
     CU_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kSmem));
@@ -402,18 +402,19 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
     fp.band_rows = (in.h + bands - 1) / bands;
     fp.bands = (in.h + fp.band_rows - 1) / fp.band_rows;
     fp.invert = p.inv ? 1u : 0u;
-    fp.do_ssim = d_ssim ? 1u : 0u;
+    fp.do_ssim = (d_ssim || d_moments) ? 1u : 0u;
+    fp.ssim_y0 = y0, fp.ssim_y1 = std::min(y1, in.h);
     const uint32_t items_per_frame = fp.strips * fp.bands;
-    if (d_ssim) {
+    if (fp.do_ssim) {
         NORM_TRY(ensure_buf(ctx, slot.partials, (size_t)in.frames * items_per_frame * 5 * sizeof(double)));
         fp.partials = static_cast<double *>(slot.partials.p);
     }
     const unsigned grid = grid_for(ctx, (size_t)items_per_frame * in.frames, per_sm);
     kern<<<grid, kFusedThreads, C::kSmem, slot.stream>>>(fp);
     LAUNCH_CHECK(ctx);
-    if (d_ssim) {
-        ssim_finalize_kernel<<<in.frames, 256, 0, slot.stream>>>(fp.partials, items_per_frame,
-                                                                 (double)in.w * (double)in.h, nullptr, d_ssim);
+    if (fp.do_ssim) {
+        const double npix = (double)in.w * (double)(fp.ssim_y1 - fp.ssim_y0);
+        ssim_finalize_kernel<<<in.frames, 256, 0, slot.stream>>>(fp.partials, items_per_frame, npix, d_moments, d_ssim);
         LAUNCH_CHECK(ctx);
     }
     return NORM_OK;
@@ -421,35 +422,52 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
 
 template <int R>
 norm_status launch_fused_r(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
-                           double *d_ssim) {
-    if (p.gray) return launch_fused<R, true, true>(ctx, slot, p, in, out, d_ssim);
-    if (p.front) return launch_fused<R, false, true>(ctx, slot, p, in, out, d_ssim);
-    return launch_fused<R, false, false>(ctx, slot, p, in, out, d_ssim);
+                           double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1) {
+    if (p.gray) return launch_fused<R, true, true>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+    if (p.front) return launch_fused<R, false, true>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+    return launch_fused<R, false, false>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
 }
 
 norm_status try_launch_chain_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in,
-                                   const ImgView &out, double *d_ssim, bool *fused) {
+                                   const ImgView &out, double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1,
+                                   bool *fused) {
     *fused = false;
     if (!(p.blur && p.edge) || p.sharpen || ctx->force_unfused) return NORM_OK;
     *fused = true;
     switch (p.radius) {
-    case 3: return launch_fused_r<3>(ctx, slot, p, in, out, d_ssim);
-    case 7: return launch_fused_r<7>(ctx, slot, p, in, out, d_ssim);
-    case 21: return launch_fused_r<21>(ctx, slot, p, in, out, d_ssim);
-    case 39: return launch_fused_r<39>(ctx, slot, p, in, out, d_ssim);
+    case 3: return launch_fused_r<3>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+    case 7: return launch_fused_r<7>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+    case 21: return launch_fused_r<21>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+    case 39: return launch_fused_r<39>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
     default: *fused = false; return NORM_OK;
     }
 }
 
-norm_status run_chain(norm_ctx *ctx, Slot &slot, const NormFeatureUniform *f, uint32_t flags, const ImgView &in,
-                      const ImgView &out, double *d_ssim) {
+// Row sub-view of every frame: rows [y0, y1).
+ImgView sub_rows(const ImgView &v, uint32_t y0, uint32_t y1) {
+    ImgView r = v;
+    r.ptr = v.ptr + (size_t)y0 * v.pitch;
+    r.h = y1 - y0;
+    return r;
+}
+
+// Chain in -> out; SSIM (d_ssim) and/or raw moments (d_moments) over output rows [y0, y1) only.
+norm_status run_chain_rows(norm_ctx *ctx, Slot &slot, const NormFeatureUniform *f, uint32_t flags, const ImgView &in,
+                           const ImgView &out, double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1) {
     const StagePlan p = make_plan(f, flags, /*chain=*/true);
     bool fused = false;
-    NORM_TRY(try_launch_chain_fused(ctx, slot, p, in, out, d_ssim, &fused));
+    NORM_TRY(try_launch_chain_fused(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1, &fused));
     if (fused) return NORM_OK;
     NORM_TRY(run_stages_unfused(ctx, slot, p, in, out));
-    if (d_ssim) NORM_TRY(launch_ssim(ctx, slot, out, in, nullptr, d_ssim));
+    if (d_ssim || d_moments)
+        NORM_TRY(launch_ssim(ctx, slot, sub_rows(out, y0, std::min(y1, in.h)), sub_rows(in, y0, std::min(y1, in.h)),
+                             d_moments, d_ssim));
     return NORM_OK;
+}
+
+norm_status run_chain(norm_ctx *ctx, Slot &slot, const NormFeatureUniform *f, uint32_t flags, const ImgView &in,
+                      const ImgView &out, double *d_ssim) {
+    return run_chain_rows(ctx, slot, f, flags, in, out, d_ssim, nullptr, 0, in.h);
 }
 
 norm_status ensure_results(norm_ctx *ctx, uint32_t frames) {
@@ -922,6 +940,67 @@ norm_status norm_cuda_chain_host(norm_ctx *ctx, const NormFeatureUniform *f, uin
         CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
         std::memcpy(ssim, ctx->h_results, (size_t)frames * sizeof(double));
     }
+    return NORM_OK;
+}
+
+norm_status norm_cuda_chain_band(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags, const norm_img *in,
+                                 norm_img *out, uint32_t own_row0, uint32_t own_rows, double *moments) {
+    NORM_TRY(bind(ctx));
+    NORM_TRY(check_pair(ctx, in, out, false));
+    NORM_TRY(check_uniform(ctx, f, in->v));
+    if (own_rows == 0 || (uint64_t)own_row0 + own_rows > in->v.h)
+        return fail(ctx, NORM_E_INVALID_ARG, "owned row range outside the band image");
+    double *d_m = nullptr;
+    if (moments) {
+        NORM_TRY(ensure_results(ctx, in->v.frames));
+        d_m = static_cast<double *>(ctx->results.p);
+    }
+    NORM_TRY(run_chain_rows(ctx, ctx->main, f, flags, in->v, out->v, nullptr, d_m, own_row0, own_row0 + own_rows));
+    if (moments)
+        CU_TRY(ctx, cudaMemcpyAsync(ctx->h_results, d_m, (size_t)in->v.frames * 5 * sizeof(double),
+                                    cudaMemcpyDeviceToHost, ctx->main.stream));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    if (moments) std::memcpy(moments, ctx->h_results, (size_t)in->v.frames * 5 * sizeof(double));
+    return NORM_OK;
+}
+
+norm_status norm_cuda_ipc_export(norm_ctx *ctx, const norm_img *img, uint8_t handle[64]) {
+    NORM_TRY(bind(ctx));
+    if (!img || !handle) return fail(ctx, NORM_E_INVALID_ARG, "NULL argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle is 64 bytes");
+    cudaIpcMemHandle_t h;
+    CU_TRY(ctx, cudaIpcGetMemHandle(&h, img->v.ptr));
+    std::memcpy(handle, &h, 64);
+    return NORM_OK;
+}
+
+norm_status norm_cuda_ipc_open(norm_ctx *ctx, const uint8_t handle[64], void **device_ptr) {
+    NORM_TRY(bind(ctx));
+    if (!handle || !device_ptr) return fail(ctx, NORM_E_INVALID_ARG, "NULL argument");
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, 64);
+    CU_TRY(ctx, cudaIpcOpenMemHandle(device_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return NORM_OK;
+}
+
+norm_status norm_cuda_ipc_close(norm_ctx *ctx, void *device_ptr) {
+    NORM_TRY(bind(ctx));
+    if (!device_ptr) return NORM_OK;
+    CU_TRY(ctx, cudaIpcCloseMemHandle(device_ptr));
+    return NORM_OK;
+}
+
+norm_status norm_cuda_copy_rows(norm_ctx *ctx, norm_img *dst, uint32_t dst_row, const void *src_device_ptr,
+                                size_t src_pitch, uint32_t src_row, uint32_t nrows) {
+    NORM_TRY(bind(ctx));
+    if (!dst || !src_device_ptr) return fail(ctx, NORM_E_INVALID_ARG, "NULL argument");
+    if (nrows == 0) return NORM_OK;
+    if ((uint64_t)dst_row + nrows > dst->v.h || src_pitch < (size_t)dst->v.w * 4)
+        return fail(ctx, NORM_E_INVALID_ARG, "row range outside the destination image / source pitch too small");
+    // device -> device; when src is a peer mapping (norm_cuda_ipc_open) this travels over NVLink
+    CU_TRY(ctx, cudaMemcpy2DAsync(dst->v.ptr + (size_t)dst_row * dst->v.pitch, dst->v.pitch,
+                                  static_cast<const uint8_t *>(src_device_ptr) + (size_t)src_row * src_pitch, src_pitch,
+                                  (size_t)dst->v.w * 4, nrows, cudaMemcpyDeviceToDevice, ctx->main.stream));
     return NORM_OK;
 }
 

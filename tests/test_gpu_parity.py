@@ -415,3 +415,38 @@ def test_fused_matches_unfused_large_random(ctx, oracle):
     assert np.array_equal(fused, dst.download()[0])
     assert np.array_equal(fused, oracle.sobel_s(oracle.blur_s(img, 7)))
     src.destroy(), dst.destroy(), tmp.destroy()
+
+
+@pytest.mark.parametrize("nranks", [2, 3, 5])
+def test_band_mode_emulated_ranks(ctx, oracle, nranks):
+    """configs[4] logic on one GPU: each emulated rank runs norm_cuda_chain_band on its band + halo
+    (halo rows arrive through norm_cuda_copy_rows from the 'peer' band buffers); owned rows and the
+    summed SSIM moments must equal the single-image chain and the oracle."""
+    w, h = 300, 211
+    img = smooth_rgba(w, h, seed=31)
+    for kw in (dict(blur=1, blur_radius=21, edge_detect=1), dict(grayscale=1, blur=1, blur_radius=7, edge_detect=1),
+               dict(blur=1, blur_radius=5, sharpen=1)):
+        f = uniform(w, h, **kw)
+        lays = [nb.sharding.band_layout(f, h, nranks, r) for r in range(nranks)]
+        bands = [ctx.image_create(w, l["ext_rows"], 1) for l in lays]
+        outs = [ctx.image_create(w, l["ext_rows"], 1) for l in lays]
+        for l, bimg in zip(lays, bands):  # each rank starts with its OWN rows only (halo rows poisoned)
+            ext = np.full((l["ext_rows"], w, 4), 0xAB, np.uint8)
+            ext[l["own_off"]:l["own_off"] + l["rows"]] = img[l["row0"]:l["row0"] + l["rows"]]
+            bimg.upload(ext)
+        for r, bimg in enumerate(bands):  # halo exchange
+            for (peer, prow, mine, n) in nb.sharding.halo_requests(f, h, nranks, r):
+                ctx.copy_rows(bimg, mine, bands[peer].device_ptr, bands[peer].pitch, prow, n)
+        ctx.sync()
+        total = np.zeros(5)
+        rows = []
+        for l, bimg, oimg in zip(lays, bands, outs):
+            fb = uniform(w, l["ext_rows"], **kw)
+            total += ctx.chain_band(fb, bimg, oimg, l["own_off"], l["rows"], nb.NORM_CS_RAW)[0]
+            rows.append(oimg.download()[0][l["own_off"]:l["own_off"] + l["rows"]])
+        got = np.concatenate(rows)
+        eo, es = oracle.chain(img, oracle_uniform(oracle, f), oracle.CS_RAW)
+        assert np.array_equal(got, eo), (nranks, kw)
+        assert abs(nb.ssim_from_moments(total, w * h) - es) <= SSIM_TIGHT
+        for x in bands + outs:
+            x.destroy()
