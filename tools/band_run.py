@@ -81,6 +81,7 @@ def main():
     for y in range(lay["row0"], lay["row0"] + lay["rows"], slab):
         y1 = min(y + slab, lay["row0"] + lay["rows"])
         t = gen_rows(torch, y, y1, W, device=f"cuda:{local}").contiguous()
+        torch.cuda.synchronize()  # torch's stream and the library's stream are independent
         ctx.copy_rows(src, lay["own_off"] + (y - lay["row0"]), t.data_ptr(), W * 4, 0, y1 - y)
         ctx.sync()
         del t
@@ -141,7 +142,17 @@ def main():
                 tmp.destroy()
             else:
                 got = full[lay["own_off"] + (g0 - lay["row0"]): lay["own_off"] + (g1 - lay["row0"])]
-            ok = ok and bool(np.array_equal(got, eo[g0 - lo:g1 - lo]))
+            same = bool(np.array_equal(got, eo[g0 - lo:g1 - lo]))
+            if not same and os.environ.get("BAND_DEBUG"):
+                bad = np.where((got != eo[g0 - lo:g1 - lo]).any(axis=(1, 2)))[0]
+                srow = src.download()[0][lay["own_off"] + (g0 - lay["row0"]): lay["own_off"] + (g1 - lay["row0"])]
+                print(f"rank {rank} seam {seam}: rows {g0}..{g1} bad rows {bad[:8] + g0} n={bad.size} "
+                      f"src_ok={np.array_equal(srow, strip[g0 - lo:g1 - lo])}", flush=True)
+                halo = src.download()[0]
+                for (p_, prow, mine, n) in reqs:
+                    gy = lay["ext_row0"] + mine
+                    print(f"  halo from {p_}: local {mine}+{n} global {gy}: ok={np.array_equal(halo[mine:mine + n], gen_rows(np, gy, gy + n, W))}", flush=True)
+            ok = ok and same
         oks = [None] * world
         dist.all_gather_object(oks, ok)
         ok = all(oks)
