@@ -1,0 +1,377 @@
+// Fused chain kernel, second generation: three warp groups in a software pipeline.
+//
+// Same arithmetic as chain_fused_kernel (S-form of oracle/norm_oracle.c, bit-exact), different
+// decomposition.  Work item = (frame, row band, 120-column strip); the CTA (12 warps) walks
+// down the strip in batches of RB rows with three groups working on different batches at once:
+//
+//   group A (warps 0-3)   cp.async staging of RB source rows (ClampToEdge), optional in-place
+//                         front stage, H pass: thread = (row, 12-column segment), 12 x CH
+//                         outputs in registers, every tap one FFMA2, 16-byte smem stores.
+//   group B (warps 4-7)   thread = one blurred column for ALL channels: V pass with R running
+//                         outputs per channel in registers across batches (static rotation,
+//                         RB % R == 0), quantise, intensity sqrt(r^2+g^2+b^2) -> one f32 / pixel.
+//   group C (warps 8-11)  thread = one output column: 3x3 Sobel on the intensity rows (window
+//                         kept in registers, rotated by a 3-row static unroll), RGBA8 store,
+//                         f64 SSIM moments against the source pixel (prefetched one row ahead).
+//
+// A->B hand over double-buffered f32 H planes, B->C double-buffered intensity rows; each
+// hand-off is a full/empty pair of named barriers per slot, so no group ever waits on more
+// than its neighbour.  Register budgets follow the roles (setmaxnreg): B holds 3*R
+// accumulators and takes 128 registers, A and C give theirs up (56 each).
+// Instantiated for R <= 21 on RGB (3*21 accumulators); wider radii use chain_fused_kernel.
+#pragma once
+#include "chain_kernels.cuh"
+
+namespace normk {
+
+constexpr int kC2Group = 128, kC2Threads = 3 * kC2Group;
+
+template <int R, bool GRAY>
+struct Fused2Cfg {
+    static_assert(R % 2 == 1, "odd radii");
+    static constexpr int M = (R - 1) / 2;
+    static constexpr int SW = 120;                      // output columns per strip
+    static constexpr int BW = SW + 2;                   // blurred / intensity columns (+1 Sobel halo each side)
+    static constexpr int T = 12;                        // H-pass outputs per thread
+    static constexpr int SEGS = (BW + T - 1) / T;       // 11
+    static constexpr int HS = (BW + 3) / 4 * 4;         // 124: H plane row stride = columns actually stored
+    static constexpr int HL = ((M + 1) + 3) / 4 * 4;    // staged left halo, 16-byte chunks
+    static constexpr int OFF0 = HL - 1 - M;             // staged column of blurred column 0's first tap
+    static constexpr int SRCW = (OFF0 + HS + R - 1 + 3) / 4 * 4;
+    static constexpr int STG_STRIDE = SRCW;             // words, multiple of 4
+    static constexpr int RB = R * ((16 + R - 1) / R);   // rows per batch, multiple of R
+    static constexpr int CH = GRAY ? 1 : 3;
+    static constexpr int IS = 128;                      // intensity row stride
+    static constexpr size_t kStgBytes = (size_t)RB * STG_STRIDE * 4;
+    static constexpr size_t kHbBytes = (size_t)CH * RB * HS * 4;
+    static constexpr size_t kIstBytes = (size_t)RB * IS * 4;
+    // + 64 words of slack: the last H segment's unused outputs read a few words past a staged row
+    static constexpr size_t kSmem = 2 * kStgBytes + 256 + 2 * kHbBytes + 2 * kIstBytes + 256 * 4 * 2 + 256;
+    static_assert(T % 4 == 0 && HS % 4 == 0, "16-byte H stores");
+};
+
+enum {
+    kB2Full0 = 1, kB2Full1 = 2, kB2Empty0 = 3, kB2Empty1 = 4,      // A <-> B: H planes
+    kB2IFull0 = 5, kB2IFull1 = 6, kB2IEmpty0 = 7, kB2IEmpty1 = 8,  // B <-> C: intensity rows
+    kB2A = 9, kB2C = 10
+};
+
+template <int R, bool GRAY, bool FRONT>
+__global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __grid_constant__ FusedParams p) {
+    using C = Fused2Cfg<R, GRAY>;
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    __shared__ double red[5][4];
+    uint32_t *stg_base = reinterpret_cast<uint32_t *>(smem_raw);
+    float *Hb_base = reinterpret_cast<float *>(smem_raw + 2 * C::kStgBytes + 256);
+    float *Ist_base = reinterpret_cast<float *>(smem_raw + 2 * C::kStgBytes + 256 + 2 * C::kHbBytes);
+    float *lumaLut = reinterpret_cast<float *>(smem_raw + 2 * C::kStgBytes + 256 + 2 * C::kHbBytes + 2 * C::kIstBytes);
+    float *intLut = lumaLut + 256;
+    uint8_t *flut = reinterpret_cast<uint8_t *>(intLut + 256);
+    constexpr int kHbFloats = C::CH * C::RB * C::HS;
+    constexpr int kIstFloats = C::RB * C::IS;
+
+    const int tid = threadIdx.x;
+    const int W = (int)p.in.w, Himg = (int)p.in.h;
+
+    if (tid < 256) {
+        const float c = (float)tid;
+        lumaLut[tid] = __fadd_rn(__fadd_rn(__fmul_rn(c, kLumaR), __fmul_rn(c, kLumaG)), __fmul_rn(c, kLumaB));
+        intLut[tid] = __fsqrt_rn(__fmaf_rn(c, c, __fmaf_rn(c, c, __fmul_rn(c, c))));
+        flut[tid] = p.lut.v[tid];
+    }
+    __syncthreads();
+
+    const uint32_t items_per_frame = p.strips * p.bands;
+    const size_t total = (size_t)items_per_frame * p.in.frames;
+    uint32_t g = 0;  // running batch counter: buffer slot = g & 1, identical sequence in all groups
+
+// per-item geometry, identical in the three groups
+#define C2_ITEM_GEOMETRY()                                                                              \
+    const uint32_t f = (uint32_t)(item / items_per_frame);                                              \
+    const uint32_t irem = (uint32_t)(item - (size_t)f * items_per_frame);                               \
+    const int band = (int)(irem / p.strips), strip = (int)(irem - (uint32_t)band * p.strips);           \
+    const int x0 = strip * C::SW;                                                                       \
+    const int ya = band * (int)p.band_rows, yb = min(ya + (int)p.band_rows, Himg);                      \
+    const int o_lo = max(ya - 1, 0), o_hi = min(yb, Himg - 1); /* blurred rows needed */                \
+    const int NB = o_hi - o_lo + 1;                                                                     \
+    const int Q = NB + R - 1; /* rows of the clamped source sequence s(q) = clamp(o_lo - M + q) */      \
+    const int nbatch = (Q + C::RB - 1) / C::RB;                                                         \
+    (void)x0, (void)NB
+
+    if (tid < kC2Group) {
+        // =========================== group A: staging + H pass ===========================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(56));
+        constexpr int NC4 = C::SRCW / 4;           // 16-byte chunks per staged row
+        constexpr int NRG = kC2Group / NC4;        // staging row groups (threads beyond NRG*NC4 idle)
+        const int st_c4 = tid % NC4, st_rg = tid / NC4;
+
+        for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
+            C2_ITEM_GEOMETRY();
+            const uint8_t *in_frame = p.in.ptr + (size_t)f * p.in.frame_stride;
+            const int st_x = x0 - C::HL + 4 * st_c4;
+            const bool st_vec = st_x >= 0 && st_x + 3 <= W - 1;
+            const int xc0 = clampi(st_x, 0, W - 1), xc1 = clampi(st_x + 1, 0, W - 1), xc2 = clampi(st_x + 2, 0, W - 1),
+                      xc3 = clampi(st_x + 3, 0, W - 1);
+
+            // cp.async one batch of source rows (ClampToEdge in x and y) into staging buffer `buf`
+            auto stage_issue = [&](int bb, int buf) {
+                if (st_rg < NRG) {
+                    const uint32_t d0 = (uint32_t)__cvta_generic_to_shared(stg_base + buf * (C::RB * C::STG_STRIDE) + 4 * st_c4);
+                    for (int j = st_rg; j < C::RB; j += NRG) {
+                        const int sy = clampi(o_lo - C::M + bb * C::RB + j, 0, Himg - 1);
+                        const uint32_t *row = reinterpret_cast<const uint32_t *>(in_frame + (size_t)sy * p.in.pitch);
+                        const uint32_t d = d0 + j * (C::STG_STRIDE * 4);
+                        if (st_vec) {
+                            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(row + st_x) : "memory");
+                        } else {
+                            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(row + xc0) : "memory");
+                            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 4), "l"(row + xc1) : "memory");
+                            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 8), "l"(row + xc2) : "memory");
+                            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 12), "l"(row + xc3) : "memory");
+                        }
+                    }
+                }
+                asm volatile("cp.async.commit_group;" ::: "memory");
+            };
+
+            bar_sync(kB2A, kC2Group);  // previous item's last H pass is done with the staging buffers
+            stage_issue(0, 0);
+
+            for (int b = 0; b < nbatch; ++b, ++g) {
+                uint32_t *stg = stg_base + (b & 1) * (C::RB * C::STG_STRIDE);
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
+                bar_sync(kB2A, kC2Group);
+                if (b + 1 < nbatch) stage_issue(b + 1, (b + 1) & 1);
+                if (FRONT) {
+                    if (st_rg < NRG) {
+                        for (int j = st_rg; j < C::RB; j += NRG) {
+                            uint4 *cell = reinterpret_cast<uint4 *>(stg + j * C::STG_STRIDE + 4 * st_c4);
+                            uint4 v = *cell;
+                            uint32_t *pv = &v.x;
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                uint32_t r = flut[pv[e] & 0xffu], gg = flut[(pv[e] >> 8) & 0xffu],
+                                         bb = flut[(pv[e] >> 16) & 0xffu];
+                                if (GRAY) {
+                                    r = quant_u8(luma_fused((float)r, (float)gg, (float)bb));
+                                    gg = bb = r;
+                                }
+                                if (p.invert) r = 255u - r, gg = 255u - gg, bb = 255u - bb;
+                                pv[e] = pack_rgba(r, gg, bb, pv[e] >> 24);
+                            }
+                            *cell = v;
+                        }
+                    }
+                    bar_sync(kB2A, kC2Group);
+                }
+
+                const int slot = (int)(g & 1u);
+                bar_sync(kB2Empty0 + slot, 2 * kC2Group);  // group B has released this H-plane slot
+                for (int it = tid; it < C::RB * C::SEGS; it += kC2Group) {
+                    const int seg = it % C::SEGS, j = it / C::SEGS;
+                    const uint32_t *sp = stg + j * C::STG_STRIDE + C::OFF0 + seg * C::T;
+                    constexpr int TP = C::T / 2;
+                    float2 acc2[TP][C::CH];
+#pragma unroll
+                    for (int i = 0; i < TP; ++i)
+#pragma unroll
+                        for (int c = 0; c < C::CH; ++c) acc2[i][c] = make_float2(0.0f, 0.0f);
+#pragma unroll
+                    for (int jj = 0; jj < C::T + R - 1; ++jj) {
+                        const uint32_t px = sp[jj];
+                        float cv[C::CH];
+#pragma unroll
+                        for (int c = 0; c < C::CH; ++c) cv[c] = byte_f(px, c);
+#pragma unroll
+                        for (int i = 0; i < TP; ++i) {
+                            const int k = jj - 2 * i;  // tap of output 2i; output 2i+1 takes k-1 (a zero tap adds exactly 0)
+                            if (k >= 0 && k <= R) {
+#pragma unroll
+                                for (int c = 0; c < C::CH; ++c)
+                                    acc2[i][c] = __ffma2_rn(p.tp[k], make_float2(cv[c], cv[c]), acc2[i][c]);
+                            }
+                        }
+                    }
+                    float *hp = Hb_base + slot * kHbFloats + j * C::HS + seg * C::T;
+#pragma unroll
+                    for (int c = 0; c < C::CH; ++c)
+#pragma unroll
+                        for (int i = 0; i < TP; i += 2)
+                            if (seg * C::T + 2 * i < C::HS)  // columns beyond the stored width are dropped
+                                *reinterpret_cast<float4 *>(hp + c * (C::RB * C::HS) + 2 * i) =
+                                        make_float4(acc2[i][c].x, acc2[i][c].y, acc2[i + 1][c].x, acc2[i + 1][c].y);
+                }
+                __threadfence_block();
+                bar_arrive(kB2Full0 + slot, 2 * kC2Group);
+            }
+        }
+    } else if (tid < 2 * kC2Group) {
+        // =========================== group B: V pass + quantise + intensity ===========================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(128));
+        const int bcol = tid - kC2Group;  // blurred column of the strip owned by this thread
+        const bool active = bcol < C::BW;
+
+        bar_arrive(kB2Empty0, 2 * kC2Group);  // both H-plane slots start out empty
+        bar_arrive(kB2Empty1, 2 * kC2Group);
+
+        for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
+            C2_ITEM_GEOMETRY();
+            float2 vacc2[C::CH][R / 2];  // running outputs: slots (2i, 2i+1) packed, slot R-1 alone
+            float vaccl[C::CH];
+#pragma unroll
+            for (int c = 0; c < C::CH; ++c) {
+                vaccl[c] = 0.0f;
+#pragma unroll
+                for (int i = 0; i < R / 2; ++i) vacc2[c][i] = make_float2(0.0f, 0.0f);
+            }
+            for (int b = 0; b < nbatch; ++b, ++g) {
+                const int slot = (int)(g & 1u);
+                bar_sync(kB2Full0 + slot, 2 * kC2Group);    // H planes of this batch are ready
+                bar_sync(kB2IEmpty0 + slot, 2 * kC2Group);  // group C has released this intensity slot
+                if (active) {
+                    const float *hp = Hb_base + slot * kHbFloats + bcol;
+                    float *ist = Ist_base + slot * kIstFloats + bcol;
+#pragma unroll
+                    for (int j = 0; j < C::RB; ++j) {
+                        float v[C::CH];
+#pragma unroll
+                        for (int c = 0; c < C::CH; ++c) {
+                            const float h = hp[(c * C::RB + j) * C::HS];
+                            const float2 h2 = make_float2(h, h);
+                            // slot s takes tap (j - s) mod R; one FFMA2 per slot pair
+#pragma unroll
+                            for (int i = 0; i < R / 2; ++i) {
+                                const int k = ((j - 2 * i) % R + R) % R;  // tap of slot 2i; slot 2i+1 takes k-1 (mod R)
+                                if (k >= 1)
+                                    vacc2[c][i] = __ffma2_rn(p.tp[k], h2, vacc2[c][i]);
+                                else
+                                    vacc2[c][i] = __ffma2_rn(make_float2(p.taps.t[0], p.taps.t[R - 1]), h2, vacc2[c][i]);
+                            }
+                            vaccl[c] = __fmaf_rn(p.taps.t[(j + 1) % R], h, vaccl[c]);  // slot R-1
+                            const int done = (j + 1) % R;  // the output that just took its last tap
+                            float o;
+                            if (done == R - 1) {
+                                o = vaccl[c], vaccl[c] = 0.0f;
+                            } else if (done & 1) {
+                                o = vacc2[c][done / 2].y, vacc2[c][done / 2].y = 0.0f;
+                            } else {
+                                o = vacc2[c][done / 2].x, vacc2[c][done / 2].x = 0.0f;
+                            }
+                            v[c] = round_rne(o);
+                        }
+                        float I;
+                        if (GRAY)
+                            I = intLut[__float_as_uint(__fadd_rn(v[0], 12582912.0f)) & 0xffu];
+                        else
+                            I = sqrt_rn_inrange(__fmaf_rn(v[C::CH - 1], v[C::CH - 1],
+                                                          __fmaf_rn(v[C::CH > 1 ? 1 : 0], v[C::CH > 1 ? 1 : 0], __fmul_rn(v[0], v[0]))));
+                        ist[j * C::IS] = I;
+                    }
+                }
+                __threadfence_block();
+                bar_arrive(kB2Empty0 + slot, 2 * kC2Group);   // done reading the H planes
+                bar_arrive(kB2IFull0 + slot, 2 * kC2Group);   // intensity rows of this batch are ready
+            }
+        }
+    } else {
+        // =========================== group C: Sobel + store + SSIM ===========================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(56));
+        const int tc = tid - 2 * kC2Group;  // output column of the strip
+        const int lane = tc & 31, warp = tc >> 5;
+
+        bar_arrive(kB2IEmpty0, 2 * kC2Group);  // both intensity slots start out empty
+        bar_arrive(kB2IEmpty1, 2 * kC2Group);
+
+        for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
+            C2_ITEM_GEOMETRY();
+            const int x = x0 + tc;
+            const bool writes = tc < C::SW && x < W;
+            const int xl = min(x, W - 1);  // keeps addresses valid on idle lanes
+            // intensity column of x is tc+1; ClampToEdge: column -1 reads column 0, column W reads column W-1
+            const int il = (x - 1 < 0) ? tc + 1 : tc, ic = min(tc + 1, C::IS - 1), ir = (x + 1 > W - 1) ? ic : min(tc + 2, C::IS - 1);
+            const uint8_t *ip = p.in.ptr + (size_t)f * p.in.frame_stride + (size_t)ya * p.in.pitch + (size_t)xl * 4;
+            uint32_t *op = reinterpret_cast<uint32_t *>(p.out.ptr + (size_t)f * p.out.frame_stride + (size_t)ya * p.out.pitch) + xl;
+            const bool ssim_on = p.do_ssim && writes;
+            uint32_t spx_next = *reinterpret_cast<const uint32_t *>(ip);  // source pixel of row ya (L2-resident)
+            double m5[5] = {0, 0, 0, 0, 0};
+            // 3x3 window rows as (left, centre, right) triples; w0 = row o-2, w1 = row o-1 between steps
+            float w0l = 0, w0c = 0, w0r = 0, w1l = 0, w1c = 0, w1r = 0, w2l, w2c, w2r;
+            int y = ya;  // next output row
+
+// one output row: Sobel(top, mid, bottom), store, SSIM; PREFETCH fetches the next row's source pixel
+#define C2_EMIT(TL, TC, TR, ML, MR, BL, BC, BR, PREFETCH)                                                   \
+    {                                                                                                       \
+        const uint32_t spx = spx_next;                                                                      \
+        ip += p.in.pitch;                                                                                   \
+        if (PREFETCH) spx_next = *reinterpret_cast<const uint32_t *>(ip);                                   \
+        const uint32_t cq = sobel_mag_fast(TL, TC, TR, ML, MR, BL, BC, BR);                                 \
+        if (writes) *op = cq * 0x010101u | 0xff000000u;                                                     \
+        op = reinterpret_cast<uint32_t *>(reinterpret_cast<uint8_t *>(op) + p.out.pitch);                   \
+        if (ssim_on && (uint32_t)(y - (int)p.ssim_y0) < p.ssim_y1 - p.ssim_y0) {                            \
+            const double xv = (double)lumaLut[cq], yv = (double)luma_ssim(spx);                             \
+            m5[0] += xv;                                                                                    \
+            m5[1] += yv;                                                                                    \
+            m5[2] = fma(xv, xv, m5[2]);                                                                     \
+            m5[3] = fma(yv, yv, m5[3]);                                                                     \
+            m5[4] = fma(xv, yv, m5[4]);                                                                     \
+        }                                                                                                   \
+        ++y;                                                                                                \
+    }
+
+            for (int b = 0; b < nbatch; ++b, ++g) {
+                const int slot = (int)(g & 1u);
+                // rows of this batch whose blurred output exists: n = b*RB + j - (R-1) in [0, NB)
+                const int j_lo = max(0, (R - 1) - b * C::RB), j_hi = min(C::RB, NB + (R - 1) - b * C::RB);
+                // first row of this batch that completes an OWNED output row (y = o-1 >= ya)
+                const int j_e = max(j_lo, (ya + 1 - o_lo) + (R - 1) - b * C::RB);
+                bar_sync(kB2IFull0 + slot, 2 * kC2Group);
+                const float *ist = Ist_base + slot * kIstFloats;
+                int j = j_lo;
+                // rows that only fill the window (at most two per item)
+                for (; j < min(j_e, j_hi); ++j) {
+                    const float *rp = ist + j * C::IS;
+                    w2l = rp[il], w2c = rp[ic], w2r = rp[ir];
+                    if (b * C::RB + j == R - 1) w1l = w2l, w1c = w2c, w1r = w2r;  // first blurred row: row above = itself
+                    w0l = w1l, w0c = w1c, w0r = w1r;
+                    w1l = w2l, w1c = w2c, w1r = w2r;
+                }
+                // main: three rows per trip, window registers rotate statically
+                for (; j + 3 <= j_hi; j += 3) {
+                    const float *rp = ist + j * C::IS;
+                    w2l = rp[il], w2c = rp[ic], w2r = rp[ir];
+                    C2_EMIT(w2l, w2c, w2r, w1l, w1r, w0l, w0c, w0r, true);
+                    w0l = rp[C::IS + il], w0c = rp[C::IS + ic], w0r = rp[C::IS + ir];
+                    C2_EMIT(w0l, w0c, w0r, w2l, w2r, w1l, w1c, w1r, true);
+                    w1l = rp[2 * C::IS + il], w1c = rp[2 * C::IS + ic], w1r = rp[2 * C::IS + ir];
+                    C2_EMIT(w1l, w1c, w1r, w0l, w0r, w2l, w2c, w2r, true);
+                }
+                // remainder rows
+                for (; j < j_hi; ++j) {
+                    const float *rp = ist + j * C::IS;
+                    w2l = rp[il], w2c = rp[ic], w2r = rp[ir];
+                    C2_EMIT(w2l, w2c, w2r, w1l, w1r, w0l, w0c, w0r, true);
+                    w0l = w1l, w0c = w1c, w0r = w1r;
+                    w1l = w2l, w1c = w2c, w1r = w2r;
+                }
+                __threadfence_block();
+                bar_arrive(kB2IEmpty0 + slot, 2 * kC2Group);
+            }
+            // bottom edge of the image: row H-1 reads row H (clamped) = row H-1
+            if (yb == Himg) C2_EMIT(w1l, w1c, w1r, w1l, w1r, w0l, w0c, w0r, false);
+#undef C2_EMIT
+            if (p.do_ssim) {
+#pragma unroll
+                for (int k = 0; k < 5; ++k) {
+                    const double s = warp_sum(m5[k]);
+                    if (lane == 0) red[k][warp] = s;
+                }
+                bar_sync(kB2C, kC2Group);
+                if (tc < 5) p.partials[item * 5 + tc] = ((red[tc][0] + red[tc][1]) + red[tc][2]) + red[tc][3];
+                bar_sync(kB2C, kC2Group);
+            }
+        }
+    }
+#undef C2_ITEM_GEOMETRY
+}
+
+}  // namespace normk

@@ -11,10 +11,12 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "blur_kernels.cuh"
 #include "chain_kernels.cuh"
+#include "chain2_kernels.cuh"
 #include "common.cuh"
 #include "stage_kernels.cuh"
 
@@ -65,6 +67,7 @@ struct norm_ctx {
     DevBuf results;     // per-frame moments (5) + ssim (1), doubles
     double *h_results = nullptr;
     size_t h_results_cap = 0;
+    int fused_gen = 0;           // NORM_CUDA_FUSED_GEN=1 forces the first-generation fused kernel
     bool force_unfused = false;  // NORM_CUDA_FORCE_UNFUSED=1: run the chain as separate stage kernels
 };
 
@@ -377,14 +380,17 @@ norm_status run_stages_unfused(norm_ctx *ctx, Slot &slot, const StagePlan &p, co
 
 // Fused single-pass chain kernel (chain_kernels.cuh) covers front -> blur -> Sobel (+SSIM)
 // at the templated radii; every other combination runs the stage kernels back to back.
-template <int R, bool GRAY, bool FRONT>
+template <int R, bool GRAY, bool FRONT, int GEN>
 norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
                          double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1) {
-    using C = FusedCfg<R, GRAY>;
-    auto kern = chain_fused_kernel<R, GRAY, FRONT>;
+    using C = typename std::conditional<GEN == 2, Fused2Cfg<R, GRAY>, FusedCfg<R, GRAY>>::type;
+    void (*kern)(const FusedParams) = nullptr;
+    if constexpr (GEN == 2) kern = chain_fused2_kernel<R, GRAY, FRONT>;
+    else kern = chain_fused_kernel<R, GRAY, FRONT>;
+    constexpr int kThreads = GEN == 2 ? kC2Threads : kFusedThreads;
     CU_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kSmem));
     int per_sm = 1;
-    CU_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kFusedThreads, C::kSmem));
+    CU_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, C::kSmem));
     if (per_sm < 1) per_sm = 1;
     FusedParams fp;
     std::memset(&fp, 0, sizeof(fp));
@@ -410,7 +416,7 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
         fp.partials = static_cast<double *>(slot.partials.p);
     }
     const unsigned grid = grid_for(ctx, (size_t)items_per_frame * in.frames, per_sm);
-    kern<<<grid, kFusedThreads, C::kSmem, slot.stream>>>(fp);
+    kern<<<grid, kThreads, C::kSmem, slot.stream>>>(fp);
     LAUNCH_CHECK(ctx);
     if (fp.do_ssim) {
         const double npix = (double)in.w * (double)(fp.ssim_y1 - fp.ssim_y0);
@@ -423,9 +429,17 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
 template <int R>
 norm_status launch_fused_r(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
                            double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1) {
-    if (p.gray) return launch_fused<R, true, true>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
-    if (p.front) return launch_fused<R, false, true>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
-    return launch_fused<R, false, false>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+    // second-generation kernel (column-owner consumer) where its register budget allows: R <= 21
+    if constexpr (R <= 21) {
+        if (ctx->fused_gen != 1) {
+            if (p.gray) return launch_fused<R, true, true, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+            if (p.front) return launch_fused<R, false, true, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+            return launch_fused<R, false, false, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+        }
+    }
+    if (p.gray) return launch_fused<R, true, true, 1>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+    if (p.front) return launch_fused<R, false, true, 1>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+    return launch_fused<R, false, false, 1>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
 }
 
 norm_status try_launch_chain_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in,
@@ -517,6 +531,7 @@ norm_status create_impl(int32_t device, void *ext_stream, bool use_ext, norm_ctx
     if (!ctx) return NORM_E_OOM;
     ctx->device = device;
     if (const char *e = std::getenv("NORM_CUDA_FORCE_UNFUSED")) ctx->force_unfused = e[0] == '1';
+    if (const char *e = std::getenv("NORM_CUDA_FUSED_GEN")) ctx->fused_gen = std::atoi(e);
     auto bail = [&](cudaError_t ce, const char *what) {
         g_create_error = std::string(what) + ": " + cudaGetErrorString(ce);
         norm_cuda_destroy(ctx);
