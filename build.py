@@ -38,7 +38,8 @@ def build_cuda(force=False, verbose=False):
     env = dict(os.environ)
     env.pop("CC", None)
     env.pop("CXX", None)
-    cmd = [nvcc, "-ccbin", "/usr/bin/g++"] + NVCC_FLAGS + ["-o", LIB, os.path.join(CSRC, "norm_cuda.cu")]
+    extra = os.environ.get("NORM_NVCC_EXTRA", "").split()
+    cmd = [nvcc, "-ccbin", "/usr/bin/g++"] + NVCC_FLAGS + extra + ["-o", LIB, os.path.join(CSRC, "norm_cuda.cu")]
     r = subprocess.run(cmd, capture_output=True, text=True, env=env)
     log = os.path.join(ROOT, "norm_b200", "build.log")
     with open(log, "w") as f:

@@ -25,6 +25,16 @@
 namespace normk {
 
 constexpr int kC2Group = 128, kC2Threads = 3 * kC2Group;
+// register budgets per group (setmaxnreg); they must add up to 3 x the launch allocation (80)
+#ifndef NORM_C2_T
+#define NORM_C2_T 12
+#endif
+#ifndef NORM_C2_REGS_A
+#define NORM_C2_REGS_A 56
+#define NORM_C2_REGS_B 128
+#define NORM_C2_REGS_C 56
+#endif
+static_assert(NORM_C2_REGS_A + NORM_C2_REGS_B + NORM_C2_REGS_C == 240, "register budgets must sum to 3 x 80");
 
 template <int R, bool GRAY>
 struct Fused2Cfg {
@@ -32,7 +42,7 @@ struct Fused2Cfg {
     static constexpr int M = (R - 1) / 2;
     static constexpr int SW = 120;                      // output columns per strip
     static constexpr int BW = SW + 2;                   // blurred / intensity columns (+1 Sobel halo each side)
-    static constexpr int T = 12;                        // H-pass outputs per thread
+    static constexpr int T = NORM_C2_T;                 // H-pass outputs per thread
     static constexpr int SEGS = (BW + T - 1) / T;       // 11
     static constexpr int HS = (BW + 3) / 4 * 4;         // 124: H plane row stride = columns actually stored
     static constexpr int HL = ((M + 1) + 3) / 4 * 4;    // staged left halo, 16-byte chunks
@@ -100,7 +110,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
 
     if (tid < kC2Group) {
         // =========================== group A: staging + H pass ===========================
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(56));
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(NORM_C2_REGS_A));
         constexpr int NC4 = C::SRCW / 4;           // 16-byte chunks per staged row
         constexpr int NRG = kC2Group / NC4;        // staging row groups (threads beyond NRG*NC4 idle)
         const int st_c4 = tid % NC4, st_rg = tid / NC4;
@@ -207,7 +217,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         }
     } else if (tid < 2 * kC2Group) {
         // =========================== group B: V pass + quantise + intensity ===========================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(128));
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(NORM_C2_REGS_B));
         const int bcol = tid - kC2Group;  // blurred column of the strip owned by this thread
         const bool active = bcol < C::BW;
 
@@ -275,7 +285,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         }
     } else {
         // =========================== group C: Sobel + store + SSIM ===========================
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(56));
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(NORM_C2_REGS_C));
         const int tc = tid - 2 * kC2Group;  // output column of the strip
         const int lane = tc & 31, warp = tc >> 5;
 
