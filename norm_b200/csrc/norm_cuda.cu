@@ -256,7 +256,7 @@ norm_status launch_blur(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const 
 }
 
 norm_status launch_sobel(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const ImgView &out) {
-    const uint32_t tx = (in.w + kStW - 1) / kStW, ty = (in.h + kStH - 1) / kStH;
+    const uint32_t tx = (in.w + kSobW - 1) / kSobW, ty = (in.h + kSobH - 1) / kSobH;
     const unsigned grid = grid_for(ctx, (size_t)tx * ty * in.frames, 8);
     sobel_kernel<<<grid, 256, 0, s>>>(in, out, tx, ty);
     LAUNCH_CHECK(ctx);

@@ -1,0 +1,58 @@
+#!/usr/bin/env python
+"""Times every single-stage entry point on a 1080p batch and reports algorithmic GB/s against the
+measured HBM peak (MEASURED_PEAKS.json).  Stage kernels are HBM-bound: this is their roofline check."""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+import norm_b200 as nb
+
+W, H, n = 1920, 1080, int(os.environ.get("FRAMES", 256))
+peak = 6555.5
+try:
+    peak = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))["hbm_gbs"]
+except Exception:
+    pass
+src_t = torch.randint(0, 256, (n, H, W, 4), dtype=torch.uint8, device="cuda")
+dst_t = torch.empty_like(src_t)
+torch.cuda.synchronize()
+ctx = nb.Context(0)
+src = ctx.image_wrap(src_t.data_ptr(), W, H, n, W * 4, W * 4 * H)
+dst = ctx.image_wrap(dst_t.data_ptr(), W, H, n, W * 4, W * 4 * H)
+px = n * W * H
+
+
+def timeit(name, fn, bytes_per_px, reps=5):
+    fn()
+    ctx.timer_start()
+    for _ in range(reps):
+        fn()
+    ctx.timer_stop()
+    ms = ctx.timer_elapsed_ms() / reps
+    gbs = px * bytes_per_px / ms / 1e6
+    print(f"{name:34s} {ms:8.3f} ms  {px/ms/1e6:8.1f} Gpx/s  {gbs:8.0f} GB/s  {gbs/peak*100:5.1f}% of measured HBM peak")
+    return gbs
+
+
+f = nb.FeatureUniform(W, H)
+f.raw.grayscale = 1
+timeit("front: grayscale (raw)", lambda: ctx.front(f, src, dst, nb.NORM_CS_RAW), 8)
+timeit("front: sRGB table + grayscale", lambda: ctx.front(f, src, dst, nb.NORM_CS_REFERENCE), 8)
+f2 = nb.FeatureUniform(W, H)
+f2.raw.invert = 1
+timeit("front: invert", lambda: ctx.front(f2, src, dst, nb.NORM_CS_RAW), 8)
+timeit("sobel", lambda: ctx.sobel(src, dst), 8)
+timeit("sharpen", lambda: ctx.sharpen(16, src, dst), 8)
+timeit("ssim (two images)", lambda: ctx.ssim(src, dst), 8)
+for r in (3, 7, 21):
+    timeit(f"blur r={r} (RGBA, 4 channels)", lambda: ctx.blur(r, src, dst), 8)
+# expansion: one 7680x4320 image per call, RGB8 -> RGBA8 (7 B/px) and 1-bit gray (4.125 B/px); includes the H2D of the packed scanlines
+w8, h8 = 7680, 4320
+out8 = ctx.image_create(w8, h8, 1)
+rgb = np.random.default_rng(0).integers(0, 256, size=w8 * h8 * 3, dtype=np.uint8)
+png = nb.Png(w8, h8, 8, 2, rgb)
+px = w8 * h8
+timeit("expand RGB8 8K (incl. H2D pageable)", lambda: ctx.expand_rgba8(png, nb.NORM_EXPAND_SPEC, out8, 0), 7, reps=3)
