@@ -171,6 +171,31 @@ norm_status norm_cuda_expand_rgba8(norm_ctx *ctx, const NormPngDesc *png, int32_
 norm_status norm_cuda_expand_rgba8_host(norm_ctx *ctx, const NormPngDesc *png, int32_t mode,
                                         uint8_t *out_rgba8);
 
+/* ---- scanline unfilter + Adam7 (the step before expansion) ----------------- */
+
+/* The zlib-inflated IDAT stream exactly as `ScanlineReader::new` receives it
+ * (src/png/scanline_reader.rs:15-28): per row one filter-type byte followed by the filtered
+ * bytes; for interlace == 1 the seven Adam7 pass images back to back (PNG spec 8.2). */
+typedef struct NormInflatedDesc {
+    uint32_t width, height;
+    uint8_t bit_depth, color_type, interlace, _reserved;
+    const uint8_t *data;
+    size_t len;
+} NormInflatedDesc;
+
+/* Replaces ScanlineReader::read_lines (src/png/scanline_reader.rs:30-168; Adam7 geometry
+ * src/png/interlace.rs:35-83): undoes the None/Sub/Up/Average/Paeth filters and the interlacing
+ * on the GPU and returns `Png::pixel_buffer` (height * ceil(width*channels*bit_depth/8) bytes,
+ * raster order) in host memory.  PNG-spec behaviour for the cases the reference leaves
+ * unimplemented (interlaced Up/Average/Paeth, sub-byte depths).  NORM_E_INVALID_ARG for a
+ * filter byte > 4 ("Unrecognized filter method", grammar.rs:48-62) or a wrong stream length. */
+norm_status norm_cuda_unfilter(norm_ctx *ctx, const NormInflatedDesc *inflated, uint8_t *pixel_buffer);
+/* Unfilter and expand without the pixel_buffer ever leaving the device: inflated stream in,
+ * RGBA8 in frame `frame` of `out` (ScanlineReader::read_lines + ImageExt::rgba8 in one call). */
+norm_status norm_cuda_unfilter_expand_rgba8(norm_ctx *ctx, const NormInflatedDesc *inflated, const uint8_t *plte,
+                                            int32_t n_plte, const uint8_t *trns, int32_t n_trns, int32_t mode,
+                                            norm_img *out, uint32_t frame);
+
 /* ---- effects ------------------------------------------------------------------------ */
 
 /* One frame of the reference renderer, headless: EffectPipeline::execute

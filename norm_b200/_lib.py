@@ -29,6 +29,14 @@ class NormFeatureUniform(C.Structure):
 assert C.sizeof(NormFeatureUniform) == 112
 
 
+class NormInflatedDesc(C.Structure):
+    _fields_ = [
+        ("width", C.c_uint32), ("height", C.c_uint32),
+        ("bit_depth", C.c_uint8), ("color_type", C.c_uint8), ("interlace", C.c_uint8), ("_reserved", C.c_uint8),
+        ("data", C.c_void_p), ("len", C.c_size_t),
+    ]
+
+
 class NormPngDesc(C.Structure):
     _fields_ = [
         ("width", C.c_uint32), ("height", C.c_uint32),
@@ -69,6 +77,8 @@ PROTOTYPES = {
     "norm_cuda_host_free": (None, [_vp, _vp]),
     "norm_cuda_expand_rgba8": (_i32, [_vp, C.POINTER(NormPngDesc), _i32, _vp, _u32]),
     "norm_cuda_expand_rgba8_host": (_i32, [_vp, C.POINTER(NormPngDesc), _i32, _vp]),
+    "norm_cuda_unfilter": (_i32, [_vp, C.POINTER(NormInflatedDesc), _vp]),
+    "norm_cuda_unfilter_expand_rgba8": (_i32, [_vp, C.POINTER(NormInflatedDesc), _vp, _i32, _vp, _i32, _i32, _vp, _u32]),
     "norm_cuda_effects": (_i32, [_vp, _fu, _u32, _vp, _vp]),
     "norm_cuda_chain": (_i32, [_vp, _fu, _u32, _vp, _vp, _dp]),
     "norm_cuda_chain_async": (_i32, [_vp, _fu, _u32, _vp, _vp, _vp]),

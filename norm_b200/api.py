@@ -18,7 +18,7 @@ import numpy as np
 
 from . import _lib
 from ._lib import (NORM_CS_RAW, NORM_CS_REFERENCE, NORM_EXPAND_COMPAT, NORM_EXPAND_SPEC, NORM_OK,
-                   NormFeatureUniform, NormPngDesc)
+                   NormFeatureUniform, NormInflatedDesc, NormPngDesc)
 
 
 class NormError(RuntimeError):
@@ -234,6 +234,32 @@ class Context:
         d = png.desc()
         self._ok(self.lib.norm_cuda_expand_rgba8_host(self.h, C.byref(d), mode, out.ctypes.data))
         return out
+
+    # -- unfilter (ScanlineReader::read_lines on the GPU)
+    @staticmethod
+    def _inflated(width, height, bit_depth, color_type, interlace, data):
+        d = NormInflatedDesc()
+        d.width, d.height, d.bit_depth, d.color_type, d.interlace = width, height, bit_depth, color_type, interlace
+        buf = np.ascontiguousarray(np.frombuffer(bytes(data), np.uint8))
+        d.data, d.len = buf.ctypes.data, buf.size
+        return d, buf
+
+    def unfilter(self, width, height, bit_depth, color_type, interlace, inflated):
+        """inflated IDAT stream -> pixel_buffer (numpy uint8), scanline_reader.rs:30-168."""
+        ch = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[color_type]
+        out = np.empty(height * ((width * ch * bit_depth + 7) // 8), np.uint8)
+        d, keep = self._inflated(width, height, bit_depth, color_type, interlace, inflated)
+        self._ok(self.lib.norm_cuda_unfilter(self.h, C.byref(d), out.ctypes.data))
+        return out
+
+    def unfilter_expand(self, width, height, bit_depth, color_type, interlace, inflated, mode, out, frame=0,
+                        plte=None, trns=None):
+        d, keep = self._inflated(width, height, bit_depth, color_type, interlace, inflated)
+        pl = None if plte is None or len(plte) == 0 else np.ascontiguousarray(plte, np.uint8)
+        tr = None if trns is None or len(trns) == 0 else np.ascontiguousarray(trns, np.uint8)
+        self._ok(self.lib.norm_cuda_unfilter_expand_rgba8(
+            self.h, C.byref(d), pl.ctypes.data if pl is not None else None, pl.size // 3 if pl is not None else 0,
+            tr.ctypes.data if tr is not None else None, tr.size if tr is not None else 0, mode, out.handle, frame))
 
     # -- effects
     @staticmethod

@@ -19,6 +19,7 @@
 #include "chain2_kernels.cuh"
 #include "common.cuh"
 #include "stage_kernels.cuh"
+#include "unfilter_kernels.cuh"
 
 using namespace normk;
 
@@ -64,6 +65,9 @@ struct norm_ctx {
     std::string err;
     uint64_t launches = 0;
     DevBuf raw;         // expansion: packed scanlines
+    DevBuf flip_tmp;    // effects: pre-flip frame
+    DevBuf inflated, passes;  // unfilter: filtered stream, unfiltered Adam7 pass images
+    int32_t *d_status = nullptr;
     DevBuf results;     // per-frame moments (5) + ssim (1), doubles
     double *h_results = nullptr;
     size_t h_results_cap = 0;
@@ -619,6 +623,10 @@ void norm_cuda_destroy(norm_ctx *ctx) {
     free_slot(ctx->main);
     for (auto &s : ctx->pipe) free_slot(s);
     free_buf(ctx->raw);
+    free_buf(ctx->flip_tmp);
+    free_buf(ctx->inflated);
+    free_buf(ctx->passes);
+    if (ctx->d_status) cudaFree(ctx->d_status);
     free_buf(ctx->results);
     if (ctx->h_results) cudaFreeHost(ctx->h_results);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
@@ -806,7 +814,8 @@ static bool valid_depth(int ct, int bd) {
     }
 }
 
-static norm_status expand_to(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, const ImgView &out, uint32_t frame) {
+static norm_status expand_impl(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, const ImgView &out, uint32_t frame,
+                               bool pixels_on_device) {
     if (!png || !png->pixels) return fail(ctx, NORM_E_INVALID_ARG, "png descriptor / pixels is NULL");
     const int ct = png->color_type, bd = png->bit_depth;
     if (!channels_of(ct) || !valid_depth(ct, bd)) return fail(ctx, NORM_E_INVALID_ARG, "invalid colour type / bit depth");
@@ -824,12 +833,14 @@ static norm_status expand_to(norm_ctx *ctx, const NormPngDesc *png, int32_t mode
     const size_t rowb = ((size_t)png->width * channels_of(ct) * bd + 7) / 8;
     if (png->len < rowb * png->height) return fail(ctx, NORM_E_INVALID_ARG, "pixel buffer shorter than height*row_bytes");
 
-    NORM_TRY(ensure_buf(ctx, ctx->raw, align_up(rowb * png->height, 256)));
-    CU_TRY(ctx, cudaMemcpyAsync(ctx->raw.p, png->pixels, rowb * png->height, cudaMemcpyHostToDevice, ctx->main.stream));
+    if (!pixels_on_device) {
+        NORM_TRY(ensure_buf(ctx, ctx->raw, align_up(rowb * png->height, 256)));
+        CU_TRY(ctx, cudaMemcpyAsync(ctx->raw.p, png->pixels, rowb * png->height, cudaMemcpyHostToDevice, ctx->main.stream));
+    }
 
     ExpandParams p;
     std::memset(&p, 0, sizeof(p));
-    p.src = static_cast<const uint8_t *>(ctx->raw.p);
+    p.src = pixels_on_device ? png->pixels : static_cast<const uint8_t *>(ctx->raw.p);
     p.src_row_bytes = rowb;
     p.w = png->width, p.h = png->height;
     p.bit_depth = bd, p.color_type = ct, p.mode = mode;
@@ -859,6 +870,13 @@ static norm_status expand_to(norm_ctx *ctx, const NormPngDesc *png, int32_t mode
     return NORM_OK;
 }
 
+static norm_status expand_to(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, const ImgView &out, uint32_t frame) {
+    return expand_impl(ctx, png, mode, out, frame, false);
+}
+static norm_status expand_from_device(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, const ImgView &out, uint32_t frame) {
+    return expand_impl(ctx, png, mode, out, frame, true);
+}
+
 norm_status norm_cuda_expand_rgba8(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, norm_img *out, uint32_t frame) {
     NORM_TRY(bind(ctx));
     if (!out) return fail(ctx, NORM_E_INVALID_ARG, "out is NULL");
@@ -880,6 +898,106 @@ norm_status norm_cuda_expand_rgba8_host(norm_ctx *ctx, const NormPngDesc *png, i
     return NORM_OK;
 }
 
+// ---- unfilter -------------------------------------------------------------
+
+static void adam7_sizes(uint32_t w, uint32_t h, uint32_t pw[7], uint32_t ph[7]) {
+    static const uint32_t x0[7] = {0, 4, 0, 2, 0, 1, 0}, y0[7] = {0, 0, 4, 0, 2, 0, 1};
+    static const uint32_t dx[7] = {8, 8, 4, 4, 2, 2, 1}, dy[7] = {8, 8, 8, 4, 4, 2, 2};
+    for (int p = 0; p < 7; ++p) {
+        pw[p] = w > x0[p] ? (w - x0[p] + dx[p] - 1) / dx[p] : 0;
+        ph[p] = h > y0[p] ? (h - y0[p] + dy[p] - 1) / dy[p] : 0;
+    }
+}
+
+// Uploads the inflated stream, undoes the scanline filters (and Adam7) on the GPU and leaves the
+// raster pixel_buffer in ctx->raw (device).  *row_bytes_out receives its row stride.
+static norm_status unfilter_to_device(norm_ctx *ctx, const NormInflatedDesc *d, size_t *row_bytes_out) {
+    if (!d || !d->data) return fail(ctx, NORM_E_INVALID_ARG, "inflated descriptor / data is NULL");
+    const int ct = d->color_type, bd = d->bit_depth;
+    if (!channels_of(ct) || !valid_depth(ct, bd)) return fail(ctx, NORM_E_INVALID_ARG, "invalid colour type / bit depth");
+    if (d->width == 0 || d->height == 0 || d->interlace > 1) return fail(ctx, NORM_E_INVALID_ARG, "bad dimensions / interlace");
+    const uint32_t w = d->width, h = d->height, bits = (uint32_t)channels_of(ct) * bd;
+    auto rowb = [&](uint32_t ww) { return ((size_t)ww * bits + 7) / 8; };
+    const uint32_t bpp = std::max(1u, bits / 8);
+    uint32_t pw[7] = {w, 0, 0, 0, 0, 0, 0}, ph[7] = {h, 0, 0, 0, 0, 0, 0};
+    int npass = 1;
+    if (d->interlace) adam7_sizes(w, h, pw, ph), npass = 7;
+    size_t need = 0, pass_bytes = 0;
+    for (int p = 0; p < npass; ++p)
+        if (pw[p] && ph[p]) need += (size_t)ph[p] * (1 + rowb(pw[p])), pass_bytes += align_up((size_t)ph[p] * rowb(pw[p]), 16);
+    if (d->len != need) return fail(ctx, NORM_E_INVALID_ARG, "inflated length does not match the image geometry");
+    const size_t out_bytes = rowb(w) * h;
+    NORM_TRY(ensure_buf(ctx, ctx->inflated, align_up(need, 256)));
+    NORM_TRY(ensure_buf(ctx, ctx->raw, align_up(out_bytes, 256)));
+    if (d->interlace) NORM_TRY(ensure_buf(ctx, ctx->passes, align_up(pass_bytes, 256)));
+    if (!ctx->d_status) CU_TRY(ctx, cudaMalloc(&ctx->d_status, sizeof(int32_t)));
+    cudaStream_t s = ctx->main.stream;
+    CU_TRY(ctx, cudaMemsetAsync(ctx->d_status, 0, sizeof(int32_t), s));
+    CU_TRY(ctx, cudaMemcpyAsync(ctx->inflated.p, d->data, need, cudaMemcpyHostToDevice, s));
+
+    UnfilterParams up;
+    std::memset(&up, 0, sizeof(up));
+    up.status = ctx->d_status;
+    DeinterlaceParams dp;
+    std::memset(&dp, 0, sizeof(dp));
+    size_t soff = 0, poff = 0;
+    for (int p = 0; p < npass; ++p) {
+        UnfilterPass &ps = up.pass[up.npass];
+        if (!pw[p] || !ph[p]) continue;
+        ps.src = static_cast<const uint8_t *>(ctx->inflated.p) + soff;
+        ps.dst = d->interlace ? static_cast<uint8_t *>(ctx->passes.p) + poff : static_cast<uint8_t *>(ctx->raw.p);
+        ps.rows = ph[p], ps.row_bytes = (uint32_t)rowb(pw[p]), ps.bpp = bpp;
+        dp.pass_px[p] = ps.dst, dp.pass_row_bytes[p] = ps.row_bytes;
+        soff += (size_t)ph[p] * (1 + rowb(pw[p]));
+        poff += align_up((size_t)ph[p] * rowb(pw[p]), 16);
+        ++up.npass;
+    }
+    unfilter_kernel<<<up.npass, kUnfThreads, 0, s>>>(up);
+    LAUNCH_CHECK(ctx);
+    if (d->interlace) {
+        for (int p = 0; p < 7; ++p)
+            if (!dp.pass_px[p]) dp.pass_px[p] = static_cast<const uint8_t *>(ctx->passes.p);  // empty pass: never read
+        dp.dst = static_cast<uint8_t *>(ctx->raw.p);
+        dp.w = w, dp.h = h, dp.row_bytes = (uint32_t)rowb(w), dp.bits = bits;
+        deinterlace_kernel<<<grid_for(ctx, (out_bytes + 255) / 256, 8), 256, 0, s>>>(dp);
+        LAUNCH_CHECK(ctx);
+    }
+    int32_t st = 0;
+    CU_TRY(ctx, cudaMemcpyAsync(&st, ctx->d_status, sizeof(st), cudaMemcpyDeviceToHost, s));
+    CU_TRY(ctx, cudaStreamSynchronize(s));
+    if (st) return fail(ctx, NORM_E_INVALID_ARG, "Unrecognized filter method in the scanline stream");  // grammar.rs:48-62
+    if (row_bytes_out) *row_bytes_out = rowb(w);
+    return NORM_OK;
+}
+
+norm_status norm_cuda_unfilter(norm_ctx *ctx, const NormInflatedDesc *d, uint8_t *pixel_buffer) {
+    NORM_TRY(bind(ctx));
+    if (!pixel_buffer) return fail(ctx, NORM_E_INVALID_ARG, "pixel_buffer is NULL");
+    size_t rb = 0;
+    NORM_TRY(unfilter_to_device(ctx, d, &rb));
+    CU_TRY(ctx, cudaMemcpyAsync(pixel_buffer, ctx->raw.p, rb * d->height, cudaMemcpyDeviceToHost, ctx->main.stream));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    return NORM_OK;
+}
+
+static norm_status expand_from_device(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, const ImgView &out, uint32_t frame);
+
+norm_status norm_cuda_unfilter_expand_rgba8(norm_ctx *ctx, const NormInflatedDesc *d, const uint8_t *plte, int32_t n_plte,
+                                            const uint8_t *trns, int32_t n_trns, int32_t mode, norm_img *out, uint32_t frame) {
+    NORM_TRY(bind(ctx));
+    if (!out) return fail(ctx, NORM_E_INVALID_ARG, "out is NULL");
+    size_t rb = 0;
+    NORM_TRY(unfilter_to_device(ctx, d, &rb));
+    NormPngDesc png;
+    std::memset(&png, 0, sizeof(png));
+    png.width = d->width, png.height = d->height, png.bit_depth = d->bit_depth, png.color_type = d->color_type;
+    png.pixels = static_cast<const uint8_t *>(ctx->raw.p), png.len = rb * d->height;
+    png.plte = plte, png.n_plte = n_plte, png.trns = trns, png.n_trns = n_trns;
+    NORM_TRY(expand_from_device(ctx, &png, mode, out->v, frame));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    return NORM_OK;
+}
+
 // ---- effects ---------------------------------------------------------------------------
 
 norm_status norm_cuda_effects(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags, const norm_img *in,
@@ -888,7 +1006,19 @@ norm_status norm_cuda_effects(norm_ctx *ctx, const NormFeatureUniform *f, uint32
     NORM_TRY(check_pair(ctx, in, out, false));
     NORM_TRY(check_uniform(ctx, f, in->v));
     const StagePlan p = make_plan(f, flags, /*chain=*/false);
-    NORM_TRY(run_stages_unfused(ctx, ctx->main, p, in->v, out->v));
+    // FlipX / FlipY: sign of the transform's x / y scale (feature_uniform.rs:143-175)
+    const bool flip_x = f->transform[0][0] < 0.0f, flip_y = f->transform[1][1] < 0.0f;
+    if (!flip_x && !flip_y) {
+        NORM_TRY(run_stages_unfused(ctx, ctx->main, p, in->v, out->v));
+    } else {
+        const size_t bytes = in->v.frames * align_up((size_t)in->v.w * 4, 256) * in->v.h;
+        NORM_TRY(ensure_buf(ctx, ctx->flip_tmp, bytes));
+        const ImgView tmp = view_of(ctx->flip_tmp.p, in->v.w, in->v.h, in->v.frames);
+        NORM_TRY(run_stages_unfused(ctx, ctx->main, p, in->v, tmp));
+        const size_t items = (size_t)((in->v.w + 3) / 4) * in->v.h * in->v.frames;
+        flip_kernel<<<grid_for(ctx, (items + 255) / 256, 8), 256, 0, ctx->main.stream>>>(tmp, out->v, flip_x, flip_y);
+        LAUNCH_CHECK(ctx);
+    }
     CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
     return NORM_OK;
 }

@@ -880,6 +880,17 @@ int oracle_effects(const oracle_feature_uniform *f, int cs, const uint8_t *in, u
         oracle_sobel_s(A, w, h, out);
     else
         memcpy(out, A, nb);
+    /* FlipX / FlipY: feature_uniform.rs:143-175 flips the sign of the transform's x / y scale and
+     * vs_main (image_shader.wgsl:43-59) applies it to the quad position: the finished frame is
+     * mirrored, texture-space effects are unaffected. */
+    const int flip_x = f->transform[0][0] < 0.0f, flip_y = f->transform[1][1] < 0.0f;
+    if (flip_x || flip_y) {
+        memcpy(A, out, nb);
+        for (uint32_t y = 0; y < h; ++y)
+            for (uint32_t x = 0; x < w; ++x)
+                memcpy(out + ((size_t)y * w + x) * 4,
+                       A + ((size_t)(flip_y ? h - 1 - y : y) * w + (flip_x ? w - 1 - x : x)) * 4, 4);
+    }
     free(A);
     return ORACLE_OK;
 }

@@ -450,3 +450,24 @@ def test_band_mode_emulated_ranks(ctx, oracle, nranks):
         assert abs(nb.ssim_from_moments(total, w * h) - es) <= SSIM_TIGHT
         for x in bands + outs:
             x.destroy()
+
+
+def test_effects_flips(ctx, oracle):
+    """FlipX / FlipY (feature_uniform.rs:143-175): the finished frame is mirrored."""
+    for (w, h) in [(5, 7), (130, 70), (333, 41)]:
+        img = smooth_rgba(w, h, seed=w)
+        for fx, fy in ((1, 0), (0, 1), (1, 1)):
+            for kw in (dict(), dict(blur=1, blur_radius=7), dict(grayscale=1, edge_detect=1)):
+                f = uniform(w, h, **kw)
+                if fx:
+                    f.apply_transform("FlipX")
+                if fy:
+                    f.apply_transform("FlipY")
+                got = run_stage(ctx, lambda s, d: ctx.effects(f, s, d, nb.NORM_CS_RAW), img)[0]
+                f0 = uniform(w, h, **kw)
+                base = oracle.effects(img, oracle_uniform(oracle, f0), oracle.CS_RAW)
+                exp = base[::-1 if fy else 1, ::-1 if fx else 1]
+                assert np.array_equal(got, exp), (w, h, fx, fy, kw)
+                of = oracle_uniform(oracle, f)
+                of.transform[0][0], of.transform[1][1] = f.raw.transform[0][0], f.raw.transform[1][1]
+                assert np.array_equal(oracle.effects(img, of, oracle.CS_RAW), exp)
