@@ -58,24 +58,36 @@ __global__ void __launch_bounds__(kUnfThreads) unfilter_kernel(const __grid_cons
 #pragma unroll
         for (int i = 0; i < kUnfMaxBpp; ++i) left[i] = upleft[i] = 0;
         const uint32_t nsteps = npx + min((uint32_t)kUnfThreads, ps.rows - y0) - 1;
+        // filtered bytes (and, for thread 0 of a later block, the row above) of the pixel handled in the
+        // NEXT step are fetched one step ahead so the global-memory latency overlaps the barrier
+        uint8_t nx[kUnfMaxBpp], nu[kUnfMaxBpp];
+        auto fetch = [&](int k) {
+#pragma unroll
+            for (int i = 0; i < kUnfMaxBpp; ++i) {
+                nx[i] = nu[i] = 0;
+                const uint32_t bi = (uint32_t)k * bpp + i;
+                if (live && k >= 0 && k < (int)npx && (uint32_t)i < bpp && bi < ps.row_bytes) {
+                    nx[i] = row[1 + bi];
+                    if (t == 0 && up_row) nu[i] = up_row[bi];
+                }
+            }
+        };
         __syncthreads();  // the previous block of rows is completely written (thread 0 reads it as "up")
+        fetch(0 - t);
         for (uint32_t s = 0; s < nsteps; ++s) {
             const int k = (int)s - t;  // pixel this thread handles in this step
+            uint8_t cx[kUnfMaxBpp], cu[kUnfMaxBpp];
+#pragma unroll
+            for (int i = 0; i < kUnfMaxBpp; ++i) cx[i] = nx[i], cu[i] = nu[i];
+            fetch(k + 1);
             if (live && k >= 0 && k < (int)npx) {
-                uint8_t up[kUnfMaxBpp];
                 const uint32_t b0 = (uint32_t)k * bpp, nb = min(bpp, ps.row_bytes - b0);
 #pragma unroll
                 for (int i = 0; i < kUnfMaxBpp; ++i) {
-                    up[i] = 0;
                     if ((uint32_t)i < nb) {
-                        if (t > 0) up[i] = slot[(s + 1) & 1][t - 1][i];       // published by row y-1 in step s-1
-                        else if (up_row) up[i] = up_row[b0 + i];               // previous block's last row
-                    }
-                }
-#pragma unroll
-                for (int i = 0; i < kUnfMaxBpp; ++i) {
-                    if ((uint32_t)i < nb) {
-                        const uint32_t x = row[1 + b0 + i], a = left[i], b = up[i], c = upleft[i];
+                        // "up": published by row y-1 in step s-1, or the previous block's last row
+                        const uint32_t b = t > 0 ? slot[(s + 1) & 1][t - 1][i] : cu[i];
+                        const uint32_t x = cx[i], a = left[i], c = upleft[i];
                         uint32_t pred = 0;
                         switch (ft) {
                         case 1: pred = a; break;
@@ -88,7 +100,7 @@ __global__ void __launch_bounds__(kUnfThreads) unfilter_kernel(const __grid_cons
                         out[b0 + i] = v;
                         slot[s & 1][t][i] = v;
                         left[i] = v;
-                        upleft[i] = up[i];
+                        upleft[i] = (uint8_t)b;
                     }
                 }
             }
