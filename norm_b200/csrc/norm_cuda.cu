@@ -434,14 +434,17 @@ template <int R>
 norm_status launch_fused_r(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
                            double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1) {
     // second-generation kernel (column-owner consumer) where its register budget allows: R <= 21
+    // (group B keeps CH*R running outputs in registers: any radius on one channel, R <= 21 on RGB)
     if constexpr (R <= 21) {
         if (ctx->fused_gen != 1) {
             if (p.gray) return launch_fused<R, true, true, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
             if (p.front) return launch_fused<R, false, true, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
             return launch_fused<R, false, false, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
         }
+        if (p.gray) return launch_fused<R, true, true, 1>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+    } else {
+        if (p.gray) return launch_fused<R, true, true, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
     }
-    if (p.gray) return launch_fused<R, true, true, 1>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
     if (p.front) return launch_fused<R, false, true, 1>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
     return launch_fused<R, false, false, 1>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
 }
