@@ -818,7 +818,7 @@ static bool valid_depth(int ct, int bd) {
 }
 
 static norm_status expand_impl(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, const ImgView &out, uint32_t frame,
-                               bool pixels_on_device) {
+                               bool pixels_on_device, size_t device_row_stride = 0) {
     if (!png || !png->pixels) return fail(ctx, NORM_E_INVALID_ARG, "png descriptor / pixels is NULL");
     const int ct = png->color_type, bd = png->bit_depth;
     if (!channels_of(ct) || !valid_depth(ct, bd)) return fail(ctx, NORM_E_INVALID_ARG, "invalid colour type / bit depth");
@@ -844,7 +844,7 @@ static norm_status expand_impl(norm_ctx *ctx, const NormPngDesc *png, int32_t mo
     ExpandParams p;
     std::memset(&p, 0, sizeof(p));
     p.src = pixels_on_device ? png->pixels : static_cast<const uint8_t *>(ctx->raw.p);
-    p.src_row_bytes = rowb;
+    p.src_row_bytes = (pixels_on_device && device_row_stride) ? device_row_stride : rowb;
     p.w = png->width, p.h = png->height;
     p.bit_depth = bd, p.color_type = ct, p.mode = mode;
     if (png->plte && png->n_plte > 0) {
@@ -875,9 +875,6 @@ static norm_status expand_impl(norm_ctx *ctx, const NormPngDesc *png, int32_t mo
 
 static norm_status expand_to(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, const ImgView &out, uint32_t frame) {
     return expand_impl(ctx, png, mode, out, frame, false);
-}
-static norm_status expand_from_device(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, const ImgView &out, uint32_t frame) {
-    return expand_impl(ctx, png, mode, out, frame, true);
 }
 
 norm_status norm_cuda_expand_rgba8(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, norm_img *out, uint32_t frame) {
@@ -912,9 +909,11 @@ static void adam7_sizes(uint32_t w, uint32_t h, uint32_t pw[7], uint32_t ph[7]) 
     }
 }
 
-// Uploads the inflated stream, undoes the scanline filters (and Adam7) on the GPU and leaves the
-// raster pixel_buffer in ctx->raw (device).  *row_bytes_out receives its row stride.
-static norm_status unfilter_to_device(norm_ctx *ctx, const NormInflatedDesc *d, size_t *row_bytes_out) {
+// Uploads the inflated stream and undoes the scanline filters (and Adam7) on the GPU.  The raster
+// pixel_buffer is left in device memory: *dev_out points at it, *pitch_out is its row stride
+// (row_bytes for interlaced images, a 16-byte-aligned pitch otherwise).
+static norm_status unfilter_to_device(norm_ctx *ctx, const NormInflatedDesc *d, const uint8_t **dev_out,
+                                      size_t *pitch_out, size_t *row_bytes_out) {
     if (!d || !d->data) return fail(ctx, NORM_E_INVALID_ARG, "inflated descriptor / data is NULL");
     const int ct = d->color_type, bd = d->bit_depth;
     if (!channels_of(ct) || !valid_depth(ct, bd)) return fail(ctx, NORM_E_INVALID_ARG, "invalid colour type / bit depth");
@@ -925,14 +924,18 @@ static norm_status unfilter_to_device(norm_ctx *ctx, const NormInflatedDesc *d, 
     uint32_t pw[7] = {w, 0, 0, 0, 0, 0, 0}, ph[7] = {h, 0, 0, 0, 0, 0, 0};
     int npass = 1;
     if (d->interlace) adam7_sizes(w, h, pw, ph), npass = 7;
-    size_t need = 0, pass_bytes = 0;
+    size_t need = 0, pass_bytes = 0, ft_bytes = 0;
     for (int p = 0; p < npass; ++p)
-        if (pw[p] && ph[p]) need += (size_t)ph[p] * (1 + rowb(pw[p])), pass_bytes += align_up((size_t)ph[p] * rowb(pw[p]), 16);
+        if (pw[p] && ph[p]) {
+            need += (size_t)ph[p] * (1 + rowb(pw[p]));
+            pass_bytes += (size_t)ph[p] * align_up(rowb(pw[p]), 16);
+            ft_bytes += align_up(ph[p], 16);
+        }
     if (d->len != need) return fail(ctx, NORM_E_INVALID_ARG, "inflated length does not match the image geometry");
     const size_t out_bytes = rowb(w) * h;
     NORM_TRY(ensure_buf(ctx, ctx->inflated, align_up(need, 256)));
-    NORM_TRY(ensure_buf(ctx, ctx->raw, align_up(out_bytes, 256)));
-    if (d->interlace) NORM_TRY(ensure_buf(ctx, ctx->passes, align_up(pass_bytes, 256)));
+    NORM_TRY(ensure_buf(ctx, ctx->passes, align_up(pass_bytes, 256) + align_up(ft_bytes, 256)));
+    if (d->interlace) NORM_TRY(ensure_buf(ctx, ctx->raw, align_up(out_bytes, 256)));
     if (!ctx->d_status) CU_TRY(ctx, cudaMalloc(&ctx->d_status, sizeof(int32_t)));
     cudaStream_t s = ctx->main.stream;
     CU_TRY(ctx, cudaMemsetAsync(ctx->d_status, 0, sizeof(int32_t), s));
@@ -943,19 +946,31 @@ static norm_status unfilter_to_device(norm_ctx *ctx, const NormInflatedDesc *d, 
     up.status = ctx->d_status;
     DeinterlaceParams dp;
     std::memset(&dp, 0, sizeof(dp));
-    size_t soff = 0, poff = 0;
+    size_t soff = 0, poff = 0, foff = align_up(pass_bytes, 256);
+    uint32_t max_items = 1;
     for (int p = 0; p < npass; ++p) {
-        UnfilterPass &ps = up.pass[up.npass];
         if (!pw[p] || !ph[p]) continue;
+        UnfilterPass &ps = up.pass[up.npass++];
         ps.src = static_cast<const uint8_t *>(ctx->inflated.p) + soff;
-        ps.dst = d->interlace ? static_cast<uint8_t *>(ctx->passes.p) + poff : static_cast<uint8_t *>(ctx->raw.p);
-        ps.rows = ph[p], ps.row_bytes = (uint32_t)rowb(pw[p]), ps.bpp = bpp;
-        dp.pass_px[p] = ps.dst, dp.pass_row_bytes[p] = ps.row_bytes;
+        ps.dst = static_cast<uint8_t *>(ctx->passes.p) + poff;
+        ps.ftype = static_cast<uint8_t *>(ctx->passes.p) + foff;
+        ps.rows = ph[p], ps.row_bytes = (uint32_t)rowb(pw[p]), ps.pitch = (uint32_t)align_up(rowb(pw[p]), 16), ps.bpp = bpp;
+        dp.pass_px[p] = ps.dst, dp.pass_row_bytes[p] = ps.pitch;
         soff += (size_t)ph[p] * (1 + rowb(pw[p]));
-        poff += align_up((size_t)ph[p] * rowb(pw[p]), 16);
-        ++up.npass;
+        poff += (size_t)ph[p] * ps.pitch;
+        foff += align_up(ph[p], 16);
+        max_items = std::max<uint32_t>(max_items, (uint32_t)(((size_t)ps.pitch / 4 * ps.rows + 255) / 256));
     }
-    unfilter_kernel<<<up.npass, kUnfThreads, 0, s>>>(up);
+    unfilter_align_kernel<<<dim3(std::min<uint32_t>(max_items, (uint32_t)ctx->sm_count * 8), up.npass), 256, 0, s>>>(up);
+    LAUNCH_CHECK(ctx);
+    switch (bpp) {
+    case 1: unfilter_wave_kernel<1><<<up.npass, kUnfThreads, 0, s>>>(up); break;
+    case 2: unfilter_wave_kernel<2><<<up.npass, kUnfThreads, 0, s>>>(up); break;
+    case 3: unfilter_wave_kernel<3><<<up.npass, kUnfThreads, 0, s>>>(up); break;
+    case 4: unfilter_wave_kernel<4><<<up.npass, kUnfThreads, 0, s>>>(up); break;
+    case 6: unfilter_wave_kernel<6><<<up.npass, kUnfThreads, 0, s>>>(up); break;
+    default: unfilter_wave_kernel<8><<<up.npass, kUnfThreads, 0, s>>>(up); break;
+    }
     LAUNCH_CHECK(ctx);
     if (d->interlace) {
         for (int p = 0; p < 7; ++p)
@@ -964,39 +979,42 @@ static norm_status unfilter_to_device(norm_ctx *ctx, const NormInflatedDesc *d, 
         dp.w = w, dp.h = h, dp.row_bytes = (uint32_t)rowb(w), dp.bits = bits;
         deinterlace_kernel<<<grid_for(ctx, (out_bytes + 255) / 256, 8), 256, 0, s>>>(dp);
         LAUNCH_CHECK(ctx);
+        *dev_out = static_cast<const uint8_t *>(ctx->raw.p), *pitch_out = rowb(w);
+    } else {
+        *dev_out = up.pass[0].dst, *pitch_out = up.pass[0].pitch;
     }
     int32_t st = 0;
     CU_TRY(ctx, cudaMemcpyAsync(&st, ctx->d_status, sizeof(st), cudaMemcpyDeviceToHost, s));
     CU_TRY(ctx, cudaStreamSynchronize(s));
     if (st) return fail(ctx, NORM_E_INVALID_ARG, "Unrecognized filter method in the scanline stream");  // grammar.rs:48-62
-    if (row_bytes_out) *row_bytes_out = rowb(w);
+    *row_bytes_out = rowb(w);
     return NORM_OK;
 }
 
 norm_status norm_cuda_unfilter(norm_ctx *ctx, const NormInflatedDesc *d, uint8_t *pixel_buffer) {
     NORM_TRY(bind(ctx));
     if (!pixel_buffer) return fail(ctx, NORM_E_INVALID_ARG, "pixel_buffer is NULL");
-    size_t rb = 0;
-    NORM_TRY(unfilter_to_device(ctx, d, &rb));
-    CU_TRY(ctx, cudaMemcpyAsync(pixel_buffer, ctx->raw.p, rb * d->height, cudaMemcpyDeviceToHost, ctx->main.stream));
+    size_t rb = 0, pitch = 0;
+    const uint8_t *dev = nullptr;
+    NORM_TRY(unfilter_to_device(ctx, d, &dev, &pitch, &rb));
+    CU_TRY(ctx, cudaMemcpy2DAsync(pixel_buffer, rb, dev, pitch, rb, d->height, cudaMemcpyDeviceToHost, ctx->main.stream));
     CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
     return NORM_OK;
 }
-
-static norm_status expand_from_device(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, const ImgView &out, uint32_t frame);
 
 norm_status norm_cuda_unfilter_expand_rgba8(norm_ctx *ctx, const NormInflatedDesc *d, const uint8_t *plte, int32_t n_plte,
                                             const uint8_t *trns, int32_t n_trns, int32_t mode, norm_img *out, uint32_t frame) {
     NORM_TRY(bind(ctx));
     if (!out) return fail(ctx, NORM_E_INVALID_ARG, "out is NULL");
-    size_t rb = 0;
-    NORM_TRY(unfilter_to_device(ctx, d, &rb));
+    size_t rb = 0, pitch = 0;
+    const uint8_t *dev = nullptr;
+    NORM_TRY(unfilter_to_device(ctx, d, &dev, &pitch, &rb));
     NormPngDesc png;
     std::memset(&png, 0, sizeof(png));
     png.width = d->width, png.height = d->height, png.bit_depth = d->bit_depth, png.color_type = d->color_type;
-    png.pixels = static_cast<const uint8_t *>(ctx->raw.p), png.len = rb * d->height;
+    png.pixels = dev, png.len = pitch * d->height;
     png.plte = plte, png.n_plte = n_plte, png.trns = trns, png.n_trns = n_trns;
-    NORM_TRY(expand_from_device(ctx, &png, mode, out->v, frame));
+    NORM_TRY(expand_impl(ctx, &png, mode, out->v, frame, /*pixels_on_device=*/true, pitch));
     CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
     return NORM_OK;
 }

@@ -17,12 +17,12 @@
 namespace normk {
 
 constexpr int kUnfThreads = 512;
-constexpr int kUnfMaxBpp = 8;
 
 struct UnfilterPass {
     const uint8_t *src;   // filtered stream of this (sub-)image: rows of (1 + row_bytes) bytes
-    uint8_t *dst;         // unfiltered rows, row_bytes each
-    uint32_t rows, row_bytes, bpp;
+    uint8_t *dst;         // rows at a 16-byte-aligned pitch; first filled with the filtered bytes, unfiltered in place
+    uint8_t *ftype;       // one filter-type byte per row
+    uint32_t rows, row_bytes, pitch, bpp;
 };
 
 struct UnfilterParams {
@@ -31,6 +31,28 @@ struct UnfilterParams {
     int32_t *status;  // set to 1 if a filter-type byte is > 4
 };
 
+// Step 1 (fully parallel): strip the filter-type bytes and re-align every row to a 16-byte pitch.
+__global__ void __launch_bounds__(256) unfilter_align_kernel(const __grid_constant__ UnfilterParams p) {
+    const UnfilterPass ps = p.pass[blockIdx.y];
+    const uint32_t words = ps.pitch / 4;
+    const size_t total = (size_t)words * ps.rows;
+    for (size_t it = (size_t)blockIdx.x * blockDim.x + threadIdx.x; it < total; it += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t y = (uint32_t)(it / words), wx = (uint32_t)(it - (size_t)y * words);
+        const uint8_t *row = ps.src + (size_t)y * ((size_t)ps.row_bytes + 1);
+        uint32_t v = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t bx = 4 * wx + i;
+            if (bx < ps.row_bytes) v |= (uint32_t)row[1 + bx] << (8 * i);
+        }
+        reinterpret_cast<uint32_t *>(ps.dst + (size_t)y * ps.pitch)[wx] = v;
+        if (wx == 0) {
+            ps.ftype[y] = row[0];
+            if (row[0] > 4u) atomicExch(p.status, 1);
+        }
+    }
+}
+
 __device__ __forceinline__ uint32_t paeth_predict(uint32_t a, uint32_t b, uint32_t c) {
     // scanline_reader.rs:149-167
     const int p = (int)a + (int)b - (int)c;
@@ -38,71 +60,83 @@ __device__ __forceinline__ uint32_t paeth_predict(uint32_t a, uint32_t b, uint32
     return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
 }
 
-__global__ void __launch_bounds__(kUnfThreads) unfilter_kernel(const __grid_constant__ UnfilterParams p) {
-    __shared__ uint8_t slot[2][kUnfThreads][kUnfMaxBpp];
+__device__ __forceinline__ uint32_t byte_of(const uint4 &v, int i) {
+    const uint32_t w = i < 4 ? v.x : (i < 8 ? v.y : (i < 12 ? v.z : v.w));
+    return (w >> (8 * (i & 3))) & 0xffu;
+}
+
+// Step 2: the wavefront.  Thread r owns row r of the current block of rows and works in 16-byte
+// chunks: chunk c of row r may be reconstructed once row r-1 has finished chunk c (its bytes are the
+// "up" values, and the last BPP bytes of its chunk c-1 the "up-left" values of the first pixel), so
+// thread r runs one chunk behind thread r-1 and all threads step together.  The finished chunk is
+// handed to the next row through a double-buffered shared-memory slot and stored in place with one
+// 16-byte write; the next filtered chunk is fetched one step ahead.
+template <int BPP>
+__global__ void __launch_bounds__(kUnfThreads) unfilter_wave_kernel(const __grid_constant__ UnfilterParams p) {
+    __shared__ uint4 slot[2][kUnfThreads];
     const UnfilterPass ps = p.pass[blockIdx.x];
     if (ps.rows == 0 || ps.row_bytes == 0) return;
     const int t = threadIdx.x;
-    const uint32_t bpp = ps.bpp, npx = (ps.row_bytes + bpp - 1) / bpp;  // "pixels" = groups of bpp bytes
-    const size_t stride = (size_t)ps.row_bytes + 1;
+    const uint32_t nchunks = ps.pitch / 16;
 
     for (uint32_t y0 = 0; y0 < ps.rows; y0 += kUnfThreads) {
         const uint32_t y = y0 + t;
         const bool live = y < ps.rows;
-        const uint8_t *row = ps.src + (size_t)(live ? y : 0) * stride;
-        uint8_t *out = ps.dst + (size_t)(live ? y : 0) * ps.row_bytes;
-        const uint8_t *up_row = (live && y > 0) ? ps.dst + (size_t)(y - 1) * ps.row_bytes : nullptr;  // thread 0 of a later block
-        const uint32_t ft = live ? row[0] : 0u;
-        if (live && ft > 4u) atomicExch(p.status, 1);
-        uint8_t left[kUnfMaxBpp], upleft[kUnfMaxBpp];
+        uint4 *row = reinterpret_cast<uint4 *>(ps.dst + (size_t)(live ? y : 0) * ps.pitch);
+        const uint4 *up_row = (live && y > 0) ? reinterpret_cast<const uint4 *>(ps.dst + (size_t)(y - 1) * ps.pitch) : nullptr;
+        const uint32_t ft = live ? ps.ftype[y] : 0u;
+        uint32_t left[BPP], upleft[BPP];  // last BPP reconstructed bytes of this row / of the row above
 #pragma unroll
-        for (int i = 0; i < kUnfMaxBpp; ++i) left[i] = upleft[i] = 0;
-        const uint32_t nsteps = npx + min((uint32_t)kUnfThreads, ps.rows - y0) - 1;
-        // filtered bytes (and, for thread 0 of a later block, the row above) of the pixel handled in the
-        // NEXT step are fetched one step ahead so the global-memory latency overlaps the barrier
-        uint8_t nx[kUnfMaxBpp], nu[kUnfMaxBpp];
-        auto fetch = [&](int k) {
-#pragma unroll
-            for (int i = 0; i < kUnfMaxBpp; ++i) {
-                nx[i] = nu[i] = 0;
-                const uint32_t bi = (uint32_t)k * bpp + i;
-                if (live && k >= 0 && k < (int)npx && (uint32_t)i < bpp && bi < ps.row_bytes) {
-                    nx[i] = row[1 + bi];
-                    if (t == 0 && up_row) nu[i] = up_row[bi];
-                }
-            }
-        };
+        for (int i = 0; i < BPP; ++i) left[i] = upleft[i] = 0;
+        const uint32_t nsteps = nchunks + min((uint32_t)kUnfThreads, ps.rows - y0) - 1;
         __syncthreads();  // the previous block of rows is completely written (thread 0 reads it as "up")
-        fetch(0 - t);
+        uint4 nx = make_uint4(0, 0, 0, 0), nu = make_uint4(0, 0, 0, 0);
+        if (live && t == 0) {
+            nx = row[0];
+            if (up_row) nu = up_row[0];
+        }
         for (uint32_t s = 0; s < nsteps; ++s) {
-            const int k = (int)s - t;  // pixel this thread handles in this step
-            uint8_t cx[kUnfMaxBpp], cu[kUnfMaxBpp];
+            const int c = (int)s - t;  // chunk this thread handles in this step
+            const uint4 cx = nx, cu = nu;
+            const int cn = c + 1;
+            if (live && cn >= 0 && cn < (int)nchunks) {  // fetch the next chunk one step ahead
+                nx = row[cn];
+                if (t == 0 && up_row) nu = up_row[cn];
+            }
+            if (live && c >= 0 && c < (int)nchunks) {
+                const uint4 up = t > 0 ? slot[(s + 1) & 1][t - 1] : cu;  // published by row y-1 in step s-1
+                uint32_t o[4] = {0, 0, 0, 0};
+                // one specialised 16-byte loop per filter type (rows of a warp may differ in type, but each
+                // variant stays short); None and Up have no dependency along the row
+                auto run = [&](auto predictor) {
 #pragma unroll
-            for (int i = 0; i < kUnfMaxBpp; ++i) cx[i] = nx[i], cu[i] = nu[i];
-            fetch(k + 1);
-            if (live && k >= 0 && k < (int)npx) {
-                const uint32_t b0 = (uint32_t)k * bpp, nb = min(bpp, ps.row_bytes - b0);
-#pragma unroll
-                for (int i = 0; i < kUnfMaxBpp; ++i) {
-                    if ((uint32_t)i < nb) {
-                        // "up": published by row y-1 in step s-1, or the previous block's last row
-                        const uint32_t b = t > 0 ? slot[(s + 1) & 1][t - 1][i] : cu[i];
-                        const uint32_t x = cx[i], a = left[i], c = upleft[i];
-                        uint32_t pred = 0;
-                        switch (ft) {
-                        case 1: pred = a; break;
-                        case 2: pred = b; break;
-                        case 3: pred = (a + b) >> 1; break;
-                        case 4: pred = paeth_predict(a, b, c); break;
-                        default: break;
-                        }
-                        const uint8_t v = (uint8_t)(x + pred);
-                        out[b0 + i] = v;
-                        slot[s & 1][t][i] = v;
-                        left[i] = v;
-                        upleft[i] = (uint8_t)b;
+                    for (int i = 0; i < 16; ++i) {
+                        const uint32_t x = byte_of(cx, i), b = byte_of(up, i);
+                        const uint32_t v = (x + predictor(left[i % BPP], b, upleft[i % BPP])) & 0xffu;
+                        o[i / 4] |= v << (8 * (i & 3));
+                        left[i % BPP] = v;
+                        upleft[i % BPP] = b;
                     }
+                };
+                switch (ft) {
+                case 1: run([](uint32_t a, uint32_t, uint32_t) { return a; }); break;
+                case 2: run([](uint32_t, uint32_t b, uint32_t) { return b; }); break;
+                case 3: run([](uint32_t a, uint32_t b, uint32_t) { return (a + b) >> 1; }); break;
+                case 4: run([](uint32_t a, uint32_t b, uint32_t c) { return paeth_predict(a, b, c); }); break;
+                default: run([](uint32_t, uint32_t, uint32_t) { return 0u; }); break;
                 }
+                // left[j] / upleft[j] are indexed by (byte position in chunk) % BPP; re-base them for the
+                // next chunk, whose byte 0 sits 16 positions further (a static rotation, no-op if BPP | 16)
+                if (16 % BPP != 0) {
+                    uint32_t tl[BPP], tu[BPP];
+#pragma unroll
+                    for (int j = 0; j < BPP; ++j) tl[j] = left[(j + 16) % BPP], tu[j] = upleft[(j + 16) % BPP];
+#pragma unroll
+                    for (int j = 0; j < BPP; ++j) left[j] = tl[j], upleft[j] = tu[j];
+                }
+                const uint4 res = make_uint4(o[0], o[1], o[2], o[3]);
+                row[c] = res;  // bytes past row_bytes inside the pitch are scratch
+                slot[s & 1][t] = res;
             }
             __syncthreads();
         }
