@@ -239,6 +239,15 @@ norm_status norm_cuda_chain_band(norm_ctx *ctx, const NormFeatureUniform *f, uin
                                  const norm_img *in, norm_img *out, uint32_t own_row0, uint32_t own_rows,
                                  double *moments);
 
+/* As norm_cuda_chain_band but returns without waiting; moments_dev (device, 5 doubles per frame, may
+ * be NULL) receives the owned-row moments on the context's stream, ready for an in-place
+ * norm_nccl_allreduce_sum_f64 on that same stream (norm_cuda_stream) - no host round trip. */
+norm_status norm_cuda_chain_band_async(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags,
+                                       const norm_img *in, norm_img *out, uint32_t own_row0,
+                                       uint32_t own_rows, double *moments_dev);
+/* The context's stream as a cudaStream_t (to order the caller's own work, e.g. NCCL, with it). */
+norm_status norm_cuda_stream(norm_ctx *ctx, void **cuda_stream);
+
 /* Peer access between the one-process-per-GPU ranks: export an owned image as a 64-byte CUDA
  * IPC handle, open a neighbour's handle as a device pointer valid in this process (peer access
  * over NVLink is enabled on open), close it when done.  No reference counterpart (the

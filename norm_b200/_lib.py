@@ -84,6 +84,8 @@ PROTOTYPES = {
     "norm_cuda_chain_async": (_i32, [_vp, _fu, _u32, _vp, _vp, _vp]),
     "norm_cuda_chain_host": (_i32, [_vp, _fu, _u32, _vp, _vp, _u32, _dp]),
     "norm_cuda_chain_band": (_i32, [_vp, _fu, _u32, _vp, _vp, _u32, _u32, _dp]),
+    "norm_cuda_chain_band_async": (_i32, [_vp, _fu, _u32, _vp, _vp, _u32, _u32, _vp]),
+    "norm_cuda_stream": (_i32, [_vp, C.POINTER(_vp)]),
     "norm_cuda_ipc_export": (_i32, [_vp, _vp, _vp]),
     "norm_cuda_ipc_open": (_i32, [_vp, _vp, C.POINTER(_vp)]),
     "norm_cuda_ipc_close": (_i32, [_vp, _vp]),

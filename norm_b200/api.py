@@ -291,6 +291,15 @@ class Context:
                                                m.ctypes.data_as(C.POINTER(C.c_double)) if want_moments else None))
         return m
 
+    def chain_band_async(self, f, src, dst, own_row0, own_rows, flags=NORM_CS_REFERENCE, moments_dev=None):
+        self._ok(self.lib.norm_cuda_chain_band_async(self.h, self._raw(f), flags, src.handle, dst.handle, own_row0,
+                                                     own_rows, C.c_void_p(moments_dev) if moments_dev else None))
+
+    def stream(self):
+        p = C.c_void_p()
+        self._ok(self.lib.norm_cuda_stream(self.h, C.byref(p)))
+        return p.value or 0
+
     def ipc_export(self, img):
         h = (C.c_uint8 * 64)()
         self._ok(self.lib.norm_cuda_ipc_export(self.h, img.handle, h))

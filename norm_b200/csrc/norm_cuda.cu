@@ -1130,6 +1130,22 @@ norm_status norm_cuda_chain_band(norm_ctx *ctx, const NormFeatureUniform *f, uin
     return NORM_OK;
 }
 
+norm_status norm_cuda_chain_band_async(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags, const norm_img *in,
+                                       norm_img *out, uint32_t own_row0, uint32_t own_rows, double *moments_dev) {
+    NORM_TRY(bind(ctx));
+    NORM_TRY(check_pair(ctx, in, out, false));
+    NORM_TRY(check_uniform(ctx, f, in->v));
+    if (own_rows == 0 || (uint64_t)own_row0 + own_rows > in->v.h)
+        return fail(ctx, NORM_E_INVALID_ARG, "owned row range outside the band image");
+    return run_chain_rows(ctx, ctx->main, f, flags, in->v, out->v, nullptr, moments_dev, own_row0, own_row0 + own_rows);
+}
+
+norm_status norm_cuda_stream(norm_ctx *ctx, void **cuda_stream) {
+    if (!ctx || !cuda_stream) return NORM_E_INVALID_ARG;
+    *cuda_stream = ctx->main.stream;
+    return NORM_OK;
+}
+
 norm_status norm_cuda_ipc_export(norm_ctx *ctx, const norm_img *img, uint8_t handle[64]) {
     NORM_TRY(bind(ctx));
     if (!img || !handle) return fail(ctx, NORM_E_INVALID_ARG, "NULL argument");

@@ -97,22 +97,29 @@ def main():
     fb.raw.blur, fb.raw.blur_radius, fb.raw.edge_detect = 1, a.radius, 1
     dist.barrier()
 
+    # everything of a step is queued on the context's stream: peer halo copies, the fused chain, and the
+    # in-place NCCL all-reduce of the 5 moments in device memory; the host waits once per step
+    mom = ctx.image_create(64, 1, 1)  # 256 bytes of device memory for the moments
+    stream = ctx.stream()
+
     def step():
         for (p, prow, mine, n) in reqs:  # halo rows over NVLink
             ctx.copy_rows(src, mine, peers[p], handles[p][1], prow, n)
-        m = ctx.chain_band(fb, src, dst, lay["own_off"], lay["rows"], nb.NORM_CS_RAW)[0]
-        return comm.allreduce_moments(m)
+        ctx.chain_band_async(fb, src, dst, lay["own_off"], lay["rows"], nb.NORM_CS_RAW, mom.device_ptr)
+        comm.allreduce_device(mom.device_ptr, 5, stream)
+        ctx.sync()
 
     for _ in range(a.warmup):
-        tot = step()
+        step()
     dist.barrier()
     t0 = time.perf_counter()
     ctx.timer_start()
     for _ in range(a.steps):
-        tot = step()
+        step()
     ctx.timer_stop()
     dev_ms = ctx.timer_elapsed_ms() / a.steps
     wall_ms = (time.perf_counter() - t0) / a.steps * 1e3
+    tot = np.frombuffer(mom.download()[0].tobytes()[:40], np.float64).copy()
     tmax = torch.tensor([dev_ms, wall_ms], dtype=torch.float64)
     dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
     ssim = nb.ssim_from_moments(tot, float(W) * float(H))
@@ -166,7 +173,7 @@ def main():
     for p in peers.values():
         ctx.ipc_close(p)
     comm.close()
-    src.destroy(), dst.destroy()
+    src.destroy(), dst.destroy(), mom.destroy()
     ctx.close()
     dist.destroy_process_group()
 
