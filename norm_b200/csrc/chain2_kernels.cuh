@@ -36,21 +36,28 @@ constexpr int kC2Group = 128, kC2Threads = 3 * kC2Group;
 #endif
 static_assert(NORM_C2_REGS_A + NORM_C2_REGS_B + NORM_C2_REGS_C == 240, "register budgets must sum to 3 x 80");
 
-template <int R, bool GRAY>
+// MODE 0: front -> blur -> Sobel (+ SSIM)   one blurred channel triple -> intensity -> group C
+// MODE 1: front -> blur                     group B writes the blurred RGBA8 itself, group C idles;
+//         all four channels are blurred (image_shader.wgsl:88-103 blurs alpha too); after
+//         grayscale the three colour channels coincide, so two distinct channels (y, a) remain
+template <int R, bool GRAY, int MODE = 0>
 struct Fused2Cfg {
     static_assert(R % 2 == 1, "odd radii");
     static constexpr int M = (R - 1) / 2;
+    static constexpr int HALO = MODE == 0 ? 1 : 0;      // Sobel needs one blurred pixel around each output
     static constexpr int SW = 120;                      // output columns per strip
-    static constexpr int BW = SW + 2;                   // blurred / intensity columns (+1 Sobel halo each side)
-    static constexpr int T = NORM_C2_T;                 // H-pass outputs per thread
+    static constexpr int BW = SW + 2 * HALO;            // blurred / intensity columns
+    static constexpr int T = (MODE == 1 && !GRAY && R > 9) ? 8 : NORM_C2_T;  // H-pass outputs per thread (4-channel blur: fewer, for registers)
     static constexpr int SEGS = (BW + T - 1) / T;       // 11
     static constexpr int HS = (BW + 3) / 4 * 4;         // 124: H plane row stride = columns actually stored
-    static constexpr int HL = ((M + 1) + 3) / 4 * 4;    // staged left halo, 16-byte chunks
-    static constexpr int OFF0 = HL - 1 - M;             // staged column of blurred column 0's first tap
+    static constexpr int HL = ((M + HALO) + 3) / 4 * 4; // staged left halo, 16-byte chunks
+    static constexpr int OFF0 = HL - HALO - M;          // staged column of blurred column 0's first tap
     static constexpr int SRCW = (OFF0 + HS + R - 1 + 3) / 4 * 4;
     static constexpr int STG_STRIDE = SRCW;             // words, multiple of 4
     static constexpr int RB = R * ((16 + R - 1) / R);   // rows per batch, multiple of R
-    static constexpr int CH = GRAY ? 1 : 3;
+    static constexpr int CH = MODE == 0 ? (GRAY ? 1 : 3) : (GRAY ? 2 : 4);
+    // source byte of channel c: MODE 1 + GRAY blurs (y, alpha) = bytes (0, 3)
+    __host__ __device__ static constexpr int chan_byte(int c) { return (MODE == 1 && GRAY && c == 1) ? 3 : c; }
     static constexpr int IS = 128;                      // intensity row stride
     static constexpr size_t kStgBytes = (size_t)RB * STG_STRIDE * 4;
     static constexpr size_t kHbBytes = (size_t)CH * RB * HS * 4;
@@ -66,9 +73,90 @@ enum {
     kB2A = 9, kB2C = 10
 };
 
-template <int R, bool GRAY, bool FRONT>
+// Blur-only consumer (MODE 1): V pass for channels [C0, C0+NCH) of one blurred column per thread and a
+// store of those bytes of the RGBA8 result.  On RGBA the four channels are split between groups B and C
+// (2 x R running outputs each); after grayscale group B takes both distinct channels (y, alpha).
+template <typename C, int R, bool GRAY, int C0, int NCH, int NCONS>
+__device__ __forceinline__ void blur_only_consumer(const FusedParams &p, const float *Hb_base, int bcol, uint32_t items_per_frame,
+                                                   size_t total) {
+    constexpr int kHbFloats = C::CH * C::RB * C::HS;
+    constexpr int kParties = (1 + NCONS) * kC2Group;
+    const int W = (int)p.in.w, Himg = (int)p.in.h;
+    const bool active = bcol < C::BW;
+    uint32_t g = 0;
+    bar_arrive(kB2Empty0, kParties);  // both H-plane slots start out empty
+    bar_arrive(kB2Empty1, kParties);
+    for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
+        const uint32_t f = (uint32_t)(item / items_per_frame);
+        const uint32_t irem = (uint32_t)(item - (size_t)f * items_per_frame);
+        const int band = (int)(irem / p.strips), strip = (int)(irem - (uint32_t)band * p.strips);
+        const int x0 = strip * C::SW;
+        const int ya = band * (int)p.band_rows, yb = min(ya + (int)p.band_rows, Himg);
+        const int NB = yb - ya;  // MODE 1: blurred rows == output rows
+        const int nbatch = (NB + R - 1 + C::RB - 1) / C::RB;
+        const int bx = x0 + bcol;
+        uint8_t *orow = p.out.ptr + (size_t)f * p.out.frame_stride + (size_t)ya * p.out.pitch + (size_t)min(bx, W - 1) * 4;
+        float2 vacc2[NCH][R / 2];
+        float vaccl[NCH];
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            vaccl[c] = 0.0f;
+#pragma unroll
+            for (int i = 0; i < R / 2; ++i) vacc2[c][i] = make_float2(0.0f, 0.0f);
+        }
+        for (int b = 0; b < nbatch; ++b, ++g) {
+            const int slot = (int)(g & 1u);
+            bar_sync(kB2Full0 + slot, kParties);
+            if (active) {
+                const float *hp = Hb_base + slot * kHbFloats + bcol;
+#pragma unroll
+                for (int j = 0; j < C::RB; ++j) {
+                    uint32_t q[NCH];
+#pragma unroll
+                    for (int c = 0; c < NCH; ++c) {
+                        const float h = hp[((C0 + c) * C::RB + j) * C::HS];
+                        const float2 h2 = make_float2(h, h);
+#pragma unroll
+                        for (int i = 0; i < R / 2; ++i) {
+                            const int k = ((j - 2 * i) % R + R) % R;
+                            if (k >= 1)
+                                vacc2[c][i] = __ffma2_rn(p.tp[k], h2, vacc2[c][i]);
+                            else
+                                vacc2[c][i] = __ffma2_rn(make_float2(p.taps.t[0], p.taps.t[R - 1]), h2, vacc2[c][i]);
+                        }
+                        vaccl[c] = __fmaf_rn(p.taps.t[(j + 1) % R], h, vaccl[c]);
+                        const int done = (j + 1) % R;
+                        float o;
+                        if (done == R - 1) {
+                            o = vaccl[c], vaccl[c] = 0.0f;
+                        } else if (done & 1) {
+                            o = vacc2[c][done / 2].y, vacc2[c][done / 2].y = 0.0f;
+                        } else {
+                            o = vacc2[c][done / 2].x, vacc2[c][done / 2].x = 0.0f;
+                        }
+                        // blurred values lie in [0, 255.0001]: the 1.5*2^23 trick alone is round-half-even + clamp
+                        q[c] = __float_as_uint(__fadd_rn(o, 12582912.0f)) & 0xffu;
+                    }
+                    const int n = b * C::RB + j - (R - 1);  // output row relative to ya
+                    if (n >= 0 && n < NB && bx < W) {
+                        uint8_t *px = orow + (size_t)n * p.out.pitch;
+                        if (GRAY) {  // channels (y, alpha) -> (y, y, y, alpha)
+                            *reinterpret_cast<uint32_t *>(px) = q[0] * 0x010101u | (q[NCH - 1] << 24);
+                        } else {     // two of the four bytes
+                            *reinterpret_cast<uint16_t *>(px + C0) = (uint16_t)(q[0] | (q[NCH - 1] << 8));
+                        }
+                    }
+                }
+            }
+            __threadfence_block();
+            bar_arrive(kB2Empty0 + slot, kParties);
+        }
+    }
+}
+
+template <int R, bool GRAY, bool FRONT, int MODE = 0>
 __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __grid_constant__ FusedParams p) {
-    using C = Fused2Cfg<R, GRAY>;
+    using C = Fused2Cfg<R, GRAY, MODE>;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     __shared__ double red[5][4];
     uint32_t *stg_base = reinterpret_cast<uint32_t *>(smem_raw);
@@ -94,6 +182,9 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
     const uint32_t items_per_frame = p.strips * p.bands;
     const size_t total = (size_t)items_per_frame * p.in.frames;
     uint32_t g = 0;  // running batch counter: buffer slot = g & 1, identical sequence in all groups
+    // threads meeting at the H-plane barriers: A + B, plus C when it shares the blur-only V pass (RGBA)
+    constexpr int kNCons = (MODE == 1 && !GRAY) ? 2 : 1;
+    constexpr int kABParties = (1 + kNCons) * kC2Group;
 
 // per-item geometry, identical in the three groups
 #define C2_ITEM_GEOMETRY()                                                                              \
@@ -102,7 +193,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
     const int band = (int)(irem / p.strips), strip = (int)(irem - (uint32_t)band * p.strips);           \
     const int x0 = strip * C::SW;                                                                       \
     const int ya = band * (int)p.band_rows, yb = min(ya + (int)p.band_rows, Himg);                      \
-    const int o_lo = max(ya - 1, 0), o_hi = min(yb, Himg - 1); /* blurred rows needed */                \
+    const int o_lo = max(ya - C::HALO, 0), o_hi = min(yb - 1 + C::HALO, Himg - 1); /* blurred rows needed */ \
     const int NB = o_hi - o_lo + 1;                                                                     \
     const int Q = NB + R - 1; /* rows of the clamped source sequence s(q) = clamp(o_lo - M + q) */      \
     const int nbatch = (Q + C::RB - 1) / C::RB;                                                         \
@@ -110,7 +201,10 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
 
     if (tid < kC2Group) {
         // =========================== group A: staging + H pass ===========================
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(NORM_C2_REGS_A));
+        // blur-only mode: group C idles on the 24-register minimum and group A (4 channels) takes its share
+        if constexpr (MODE == 1 && GRAY) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(88));
+        else if constexpr (MODE == 1) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(64));
+        else asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(NORM_C2_REGS_A));
         constexpr int NC4 = C::SRCW / 4;           // 16-byte chunks per staged row
         constexpr int NRG = kC2Group / NC4;        // staging row groups (threads beyond NRG*NC4 idle)
         const int st_c4 = tid % NC4, st_rg = tid / NC4;
@@ -176,7 +270,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                 }
 
                 const int slot = (int)(g & 1u);
-                bar_sync(kB2Empty0 + slot, 2 * kC2Group);  // group B has released this H-plane slot
+                bar_sync(kB2Empty0 + slot, kABParties);  // the consumer group(s) released this H-plane slot
                 for (int it = tid; it < C::RB * C::SEGS; it += kC2Group) {
                     const int seg = it % C::SEGS, j = it / C::SEGS;
                     const uint32_t *sp = stg + j * C::STG_STRIDE + C::OFF0 + seg * C::T;
@@ -191,7 +285,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                         const uint32_t px = sp[jj];
                         float cv[C::CH];
 #pragma unroll
-                        for (int c = 0; c < C::CH; ++c) cv[c] = byte_f(px, c);
+                        for (int c = 0; c < C::CH; ++c) cv[c] = byte_f(px, C::chan_byte(c));
 #pragma unroll
                         for (int i = 0; i < TP; ++i) {
                             const int k = jj - 2 * i;  // tap of output 2i; output 2i+1 takes k-1 (a zero tap adds exactly 0)
@@ -212,11 +306,21 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                                         make_float4(acc2[i][c].x, acc2[i][c].y, acc2[i + 1][c].x, acc2[i + 1][c].y);
                 }
                 __threadfence_block();
-                bar_arrive(kB2Full0 + slot, 2 * kC2Group);
+                bar_arrive(kB2Full0 + slot, kABParties);
             }
         }
     } else if (tid < 2 * kC2Group) {
         // =========================== group B: V pass + quantise + intensity ===========================
+        if constexpr (MODE == 1) {
+            if constexpr (GRAY) {
+                asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(128));
+                blur_only_consumer<C, R, true, 0, 2, 1>(p, Hb_base, tid - kC2Group, items_per_frame, total);
+            } else {
+                asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(88));
+                blur_only_consumer<C, R, false, 0, 2, 2>(p, Hb_base, tid - kC2Group, items_per_frame, total);
+            }
+            return;
+        }
         asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(NORM_C2_REGS_B));
         const int bcol = tid - kC2Group;  // blurred column of the strip owned by this thread
         const bool active = bcol < C::BW;
@@ -269,13 +373,15 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                             }
                             v[c] = round_rne(o);
                         }
-                        float I;
-                        if (GRAY)
-                            I = intLut[__float_as_uint(__fadd_rn(v[0], 12582912.0f)) & 0xffu];
-                        else
-                            I = sqrt_rn_inrange(__fmaf_rn(v[C::CH - 1], v[C::CH - 1],
-                                                          __fmaf_rn(v[C::CH > 1 ? 1 : 0], v[C::CH > 1 ? 1 : 0], __fmul_rn(v[0], v[0]))));
-                        ist[j * C::IS] = I;
+                        {
+                            float I;
+                            if (GRAY)
+                                I = intLut[__float_as_uint(__fadd_rn(v[0], 12582912.0f)) & 0xffu];
+                            else
+                                I = sqrt_rn_inrange(__fmaf_rn(v[C::CH - 1], v[C::CH - 1],
+                                                              __fmaf_rn(v[C::CH > 1 ? 1 : 0], v[C::CH > 1 ? 1 : 0], __fmul_rn(v[0], v[0]))));
+                            ist[j * C::IS] = I;
+                        }
                     }
                 }
                 __threadfence_block();
@@ -285,6 +391,15 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         }
     } else {
         // =========================== group C: Sobel + store + SSIM ===========================
+        if constexpr (MODE == 1) {
+            if constexpr (GRAY) {
+                asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(24));  // idle: hand the registers over
+            } else {
+                asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(88));
+                blur_only_consumer<C, R, false, 2, 2, 2>(p, Hb_base, tid - 2 * kC2Group, items_per_frame, total);
+            }
+            return;
+        }
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(NORM_C2_REGS_C));
         const int tc = tid - 2 * kC2Group;  // output column of the strip
         const int lane = tc & 31, warp = tc >> 5;

@@ -337,9 +337,17 @@ StagePlan make_plan(const NormFeatureUniform *f, uint32_t flags, bool chain) {
 
 // Runs the planned stages in -> out on slot.stream using the slot's ping-pong temporaries,
 // `chunk` frames at a time so the temporaries stay small for large batches.
+norm_status try_launch_blur_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
+                                  bool *fused);
+
 norm_status run_stages_unfused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out) {
     const int n = p.count();
     if (n == 0) return copy_view(ctx, slot.stream, in, out);
+    {
+        bool fused = false;  // front -> blur as one pipelined kernel where it is instantiated
+        NORM_TRY(try_launch_blur_fused(ctx, slot, p, in, out, &fused));
+        if (fused) return NORM_OK;
+    }
     const size_t frame_bytes = align_up((size_t)in.w * 4, 256) * in.h;
     uint32_t chunk = in.frames;
     if (n > 1) {
@@ -384,14 +392,16 @@ norm_status run_stages_unfused(norm_ctx *ctx, Slot &slot, const StagePlan &p, co
 
 // Fused single-pass chain kernel (chain_kernels.cuh) covers front -> blur -> Sobel (+SSIM)
 // at the templated radii; every other combination runs the stage kernels back to back.
+// GEN 1: first-generation kernel; GEN 2: pipelined kernel, MODE 0 (blur+Sobel); GEN 3: pipelined, MODE 1 (blur only)
 template <int R, bool GRAY, bool FRONT, int GEN>
 norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
                          double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1) {
-    using C = typename std::conditional<GEN == 2, Fused2Cfg<R, GRAY>, FusedCfg<R, GRAY>>::type;
+    using C = typename std::conditional<GEN == 1, FusedCfg<R, GRAY>, Fused2Cfg<R, GRAY, (GEN == 3 ? 1 : 0)>>::type;
     void (*kern)(const FusedParams) = nullptr;
-    if constexpr (GEN == 2) kern = chain_fused2_kernel<R, GRAY, FRONT>;
+    if constexpr (GEN == 3) kern = chain_fused2_kernel<R, GRAY, FRONT, 1>;
+    else if constexpr (GEN == 2) kern = chain_fused2_kernel<R, GRAY, FRONT, 0>;
     else kern = chain_fused_kernel<R, GRAY, FRONT>;
-    constexpr int kThreads = GEN == 2 ? kC2Threads : kFusedThreads;
+    constexpr int kThreads = GEN == 1 ? kFusedThreads : kC2Threads;
     CU_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kSmem));
     int per_sm = 1;
     CU_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, C::kSmem));
@@ -447,6 +457,34 @@ norm_status launch_fused_r(norm_ctx *ctx, Slot &slot, const StagePlan &p, const 
     }
     if (p.front) return launch_fused<R, false, true, 1>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
     return launch_fused<R, false, false, 1>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+}
+
+// front -> blur with nothing after it (norm_cuda_blur, the blur effect of norm_cuda_effects, blur-only chains):
+// pipelined kernel in MODE 1.  CH*R accumulators per thread: R <= 21 on RGBA (4 channels), any R after grayscale (2).
+template <int R>
+norm_status launch_blur_only_r(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
+                               bool *fused) {
+    *fused = true;
+    if (p.gray) return launch_fused<R, true, true, 3>(ctx, slot, p, in, out, nullptr, nullptr, 0, in.h);
+    if constexpr (R <= 21) {
+        if (p.front) return launch_fused<R, false, true, 3>(ctx, slot, p, in, out, nullptr, nullptr, 0, in.h);
+        return launch_fused<R, false, false, 3>(ctx, slot, p, in, out, nullptr, nullptr, 0, in.h);
+    }
+    *fused = false;
+    return NORM_OK;
+}
+
+norm_status try_launch_blur_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
+                                  bool *fused) {
+    *fused = false;
+    if (!p.blur || p.edge || p.sharpen || ctx->force_unfused || ctx->fused_gen == 1) return NORM_OK;
+    switch (p.radius) {
+    case 3: return launch_blur_only_r<3>(ctx, slot, p, in, out, fused);
+    case 7: return launch_blur_only_r<7>(ctx, slot, p, in, out, fused);
+    case 21: return launch_blur_only_r<21>(ctx, slot, p, in, out, fused);
+    case 39: return launch_blur_only_r<39>(ctx, slot, p, in, out, fused);
+    default: return NORM_OK;
+    }
 }
 
 norm_status try_launch_chain_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in,
@@ -1200,7 +1238,12 @@ norm_status norm_cuda_front(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t
 norm_status norm_cuda_blur(norm_ctx *ctx, uint32_t radius, const norm_img *in, norm_img *out) {
     NORM_TRY(bind(ctx));
     NORM_TRY(check_pair(ctx, in, out, false));
-    NORM_TRY(launch_blur(ctx, ctx->main.stream, in->v, out->v, radius));
+    if (radius < 1 || radius > NORM_MAX_BLUR_RADIUS) return fail(ctx, NORM_E_INVALID_ARG, "blur radius outside 1..63");
+    StagePlan p;
+    bool identity;
+    make_lut(NORM_CS_RAW, 0, p.lut, identity);
+    p.blur = true, p.radius = radius;
+    NORM_TRY(run_stages_unfused(ctx, ctx->main, p, in->v, out->v));
     CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
     return NORM_OK;
 }
