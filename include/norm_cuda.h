@@ -196,6 +196,22 @@ norm_status norm_cuda_unfilter_expand_rgba8(norm_ctx *ctx, const NormInflatedDes
                                             int32_t n_plte, const uint8_t *trns, int32_t n_trns, int32_t mode,
                                             norm_img *out, uint32_t frame);
 
+/* ---- scanline filtering for the encoder (the step after the path) ---------- */
+
+/* Replaces ScanlineWriter::write / test_filters (src/png/scanline_writer.rs:22-104): per row the five
+ * filter candidates, the one with the smallest sum of output bytes wins (first minimum in the order
+ * None, Sub, Up, Average, Paeth), and the stream `filter byte + filtered row` is returned in host memory
+ * (height * (1 + row_bytes) bytes) ready for deflate.  filter_types (height bytes) may be NULL.
+ * paeth_compat = 0 uses the PNG-spec Paeth predictor; 1 reproduces the reference's `a + b + c`
+ * (scanline_writer.rs:8), whose type-4 rows no decoder can undo - parity checks only. */
+norm_status norm_cuda_filter_scanlines(norm_ctx *ctx, uint32_t width, uint32_t height, uint8_t bit_depth,
+                                       uint8_t color_type, const uint8_t *pixel_buffer, int32_t paeth_compat,
+                                       uint8_t *stream, uint8_t *filter_types);
+/* Same for frame `frame` of a device-resident RGBA8 image (colour type 6, 8 bit): an effect result can
+ * leave as PNG without its raw pixels crossing PCIe first. */
+norm_status norm_cuda_filter_image(norm_ctx *ctx, const norm_img *img, uint32_t frame, int32_t paeth_compat,
+                                   uint8_t *stream, uint8_t *filter_types);
+
 /* ---- effects ------------------------------------------------------------------------ */
 
 /* One frame of the reference renderer, headless: EffectPipeline::execute

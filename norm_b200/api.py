@@ -261,6 +261,23 @@ class Context:
             self.h, C.byref(d), pl.ctypes.data if pl is not None else None, pl.size // 3 if pl is not None else 0,
             tr.ctypes.data if tr is not None else None, tr.size if tr is not None else 0, mode, out.handle, frame))
 
+    # -- encoder-side scanline filtering (ScanlineWriter::write on the GPU)
+    def filter_scanlines(self, width, height, bit_depth, color_type, pixel_buffer, paeth_compat=0):
+        """pixel_buffer -> (stream of `filter byte + filtered row`, chosen filter per row)."""
+        ch = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[color_type]
+        rowb = (width * ch * bit_depth + 7) // 8
+        px = np.ascontiguousarray(pixel_buffer, np.uint8).reshape(-1)
+        assert px.size == rowb * height
+        stream, ft = np.empty(height * (rowb + 1), np.uint8), np.empty(height, np.uint8)
+        self._ok(self.lib.norm_cuda_filter_scanlines(self.h, width, height, bit_depth, color_type, px.ctypes.data,
+                                                     paeth_compat, stream.ctypes.data, ft.ctypes.data))
+        return stream, ft
+
+    def filter_image(self, img, frame=0, paeth_compat=0):
+        stream, ft = np.empty(img.height * (img.width * 4 + 1), np.uint8), np.empty(img.height, np.uint8)
+        self._ok(self.lib.norm_cuda_filter_image(self.h, img.handle, frame, paeth_compat, stream.ctypes.data, ft.ctypes.data))
+        return stream, ft
+
     # -- effects
     @staticmethod
     def _raw(f): return C.byref(f.raw if isinstance(f, FeatureUniform) else f)

@@ -18,6 +18,7 @@
 #include "chain_kernels.cuh"
 #include "chain2_kernels.cuh"
 #include "common.cuh"
+#include "filter_kernels.cuh"
 #include "stage_kernels.cuh"
 #include "unfilter_kernels.cuh"
 
@@ -1055,6 +1056,51 @@ norm_status norm_cuda_unfilter_expand_rgba8(norm_ctx *ctx, const NormInflatedDes
     NORM_TRY(expand_impl(ctx, &png, mode, out->v, frame, /*pixels_on_device=*/true, pitch));
     CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
     return NORM_OK;
+}
+
+// ---- encoder-side scanline filtering ---------------------------------------
+
+static norm_status filter_device_rows(norm_ctx *ctx, const uint8_t *dev_rows, size_t pitch, uint32_t rows,
+                                      uint32_t row_bytes, uint32_t bpp, int32_t paeth_compat, uint8_t *stream,
+                                      uint8_t *filter_types) {
+    const size_t out_bytes = (size_t)rows * ((size_t)row_bytes + 1);
+    NORM_TRY(ensure_buf(ctx, ctx->inflated, align_up(out_bytes, 256) + align_up(rows, 256)));
+    FilterParams fp;
+    fp.src = dev_rows, fp.src_pitch = pitch;
+    fp.dst = static_cast<uint8_t *>(ctx->inflated.p);
+    fp.ftypes = fp.dst + align_up(out_bytes, 256);
+    fp.rows = rows, fp.row_bytes = row_bytes, fp.bpp = bpp, fp.paeth_compat = paeth_compat;
+    cudaStream_t s = ctx->main.stream;
+    filter_rows_kernel<<<grid_for(ctx, (rows + 7) / 8, 8), 256, 0, s>>>(fp);
+    LAUNCH_CHECK(ctx);
+    CU_TRY(ctx, cudaMemcpyAsync(stream, fp.dst, out_bytes, cudaMemcpyDeviceToHost, s));
+    if (filter_types) CU_TRY(ctx, cudaMemcpyAsync(filter_types, fp.ftypes, rows, cudaMemcpyDeviceToHost, s));
+    CU_TRY(ctx, cudaStreamSynchronize(s));
+    return NORM_OK;
+}
+
+norm_status norm_cuda_filter_scanlines(norm_ctx *ctx, uint32_t width, uint32_t height, uint8_t bit_depth,
+                                       uint8_t color_type, const uint8_t *pixel_buffer, int32_t paeth_compat,
+                                       uint8_t *stream, uint8_t *filter_types) {
+    NORM_TRY(bind(ctx));
+    if (!pixel_buffer || !stream) return fail(ctx, NORM_E_INVALID_ARG, "NULL argument");
+    if (!channels_of(color_type) || !valid_depth(color_type, bit_depth) || width == 0 || height == 0)
+        return fail(ctx, NORM_E_INVALID_ARG, "invalid image header");
+    const uint32_t bits = (uint32_t)channels_of(color_type) * bit_depth;
+    const size_t rowb = ((size_t)width * bits + 7) / 8;
+    NORM_TRY(ensure_buf(ctx, ctx->raw, align_up(rowb * height, 256)));
+    CU_TRY(ctx, cudaMemcpyAsync(ctx->raw.p, pixel_buffer, rowb * height, cudaMemcpyHostToDevice, ctx->main.stream));
+    return filter_device_rows(ctx, static_cast<const uint8_t *>(ctx->raw.p), rowb, height, (uint32_t)rowb,
+                              std::max(1u, bits / 8), paeth_compat, stream, filter_types);
+}
+
+norm_status norm_cuda_filter_image(norm_ctx *ctx, const norm_img *img, uint32_t frame, int32_t paeth_compat,
+                                   uint8_t *stream, uint8_t *filter_types) {
+    NORM_TRY(bind(ctx));
+    if (!img || !stream) return fail(ctx, NORM_E_INVALID_ARG, "NULL argument");
+    if (frame >= img->v.frames) return fail(ctx, NORM_E_INVALID_ARG, "frame out of range");
+    return filter_device_rows(ctx, img->v.ptr + (size_t)frame * img->v.frame_stride, img->v.pitch, img->v.h,
+                              img->v.w * 4, 4, paeth_compat, stream, filter_types);
 }
 
 // ---- effects ---------------------------------------------------------------------------

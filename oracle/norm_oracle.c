@@ -324,6 +324,47 @@ done:
     return rc;
 }
 
+/* src/png/scanline_writer.rs:5-61: per row the five filter candidates, smallest sum of output bytes
+ * wins (first minimum in the order None, Sub, Up, Average, Paeth).  paeth_compat != 0 reproduces the
+ * reference's predictor p = a + b + c (scanline_writer.rs:8); 0 is the PNG-spec p = a + b - c. */
+static uint8_t paeth_enc(uint8_t oa, uint8_t ob, uint8_t oc, int compat) {
+    const int a = oa, b = ob, c = oc;
+    const int p = compat ? a + b + c : a + b - c;
+    const int pa = abs(p - a), pb = abs(p - b), pc = abs(p - c);
+    if (pa <= pb && pa <= pc) return oa;
+    if (pb <= pc) return ob;
+    return oc;
+}
+
+void oracle_filter_scanlines(const uint8_t *pixels, uint32_t rows, size_t row_bytes, size_t bpp, int paeth_compat,
+                             uint8_t *stream, uint8_t *filter_types) {
+    uint8_t *cand[5];
+    for (int k = 0; k < 5; ++k) cand[k] = (uint8_t *)malloc(row_bytes ? row_bytes : 1);
+    uint8_t *zero = (uint8_t *)calloc(row_bytes ? row_bytes : 1, 1);
+    for (uint32_t y = 0; y < rows; ++y) {
+        const uint8_t *cur = pixels + (size_t)y * row_bytes, *prev = y ? cur - row_bytes : zero;
+        uint32_t sum[5] = {0, 0, 0, 0, 0};
+        for (size_t i = 0; i < row_bytes; ++i) {
+            const uint8_t a = i >= bpp ? cur[i - bpp] : 0, b = prev[i], c = i >= bpp ? prev[i - bpp] : 0;
+            cand[0][i] = cur[i];
+            cand[1][i] = (uint8_t)(cur[i] - a);
+            cand[2][i] = (uint8_t)(cur[i] - b);
+            cand[3][i] = (uint8_t)(cur[i] - (uint8_t)(((unsigned)a + b) / 2));
+            cand[4][i] = (uint8_t)(cur[i] - paeth_enc(a, b, c, paeth_compat));
+            for (int k = 0; k < 5; ++k) sum[k] += cand[k][i];
+        }
+        int best = 0;
+        for (int k = 1; k < 5; ++k)
+            if (sum[k] < sum[best]) best = k;
+        uint8_t *out = stream + (size_t)y * (row_bytes + 1);
+        out[0] = (uint8_t)best;
+        memcpy(out + 1, cand[best], row_bytes);
+        if (filter_types) filter_types[y] = (uint8_t)best;
+    }
+    for (int k = 0; k < 5; ++k) free(cand[k]);
+    free(zero);
+}
+
 /* ------------------------------------------------------------------------------------ */
 /* Pixel expansion                                                                      */
 /* ------------------------------------------------------------------------------------ */

@@ -53,6 +53,10 @@ void oracle_png_free(oracle_png *p);
 void oracle_adam7_pass_sizes(uint32_t w, uint32_t h, uint32_t pw[7], uint32_t ph[7]);
 size_t oracle_row_bytes(uint32_t w, int color_type, int bit_depth);
 
+/* src/png/scanline_writer.rs:5-104: encoder-side filter selection.  stream = rows*(1+row_bytes) bytes. */
+void oracle_filter_scanlines(const uint8_t *pixels, uint32_t rows, size_t row_bytes, size_t bpp, int paeth_compat,
+                             uint8_t *stream, uint8_t *filter_types);
+
 /* src/png/grammar.rs:123-155 (compat) / PNG-spec semantics (spec mode).  out = 4*w*h bytes. */
 int oracle_expand_rgba8(const oracle_png *p, int mode, uint8_t *out);
 /* src/png/grammar.rs:89-121: rgb8() -- the view the reference's own tests pin. */

@@ -76,6 +76,8 @@ def lib():
         L.oracle_adam7_pass_sizes.argtypes = [C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
         L.oracle_row_bytes.argtypes = [C.c_uint32, C.c_int, C.c_int]
         L.oracle_row_bytes.restype = C.c_size_t
+        L.oracle_filter_scanlines.argtypes = [u8p, C.c_uint32, C.c_size_t, C.c_size_t, C.c_int, u8p, u8p]
+        L.oracle_filter_scanlines.restype = None
         L.oracle_expand_rgba8.argtypes = [C.POINTER(OraclePng), C.c_int, u8p]
         L.oracle_rgb8.argtypes = [C.POINTER(OraclePng), u8p]
         L.oracle_front_lut.argtypes = [C.c_int, C.c_uint32, u8p]
@@ -170,6 +172,13 @@ def rgb8(png: DecodedPng):
     if rc != OK:
         raise ValueError(f"oracle_rgb8 rc={rc}")
     return out
+
+
+def filter_scanlines(pixels, rows, row_bytes, bpp, paeth_compat=0):
+    pixels = np.ascontiguousarray(pixels, np.uint8).reshape(-1)
+    stream, ft = np.empty(rows * (row_bytes + 1), np.uint8), np.empty(rows, np.uint8)
+    lib().oracle_filter_scanlines(_u8(pixels), rows, row_bytes, bpp, paeth_compat, _u8(stream), _u8(ft))
+    return stream, ft
 
 
 def adam7_pass_sizes(w, h):

@@ -320,3 +320,52 @@ def test_effects_priority_and_chain(oracle):
     assert np.array_equal(out, exp) and abs(s - oracle.ssim(exp, img)) < 1e-12
     outs, ss = oracle.chain_batch(np.stack([img, img[::-1].copy()]), f, oracle.CS_REFERENCE)
     assert np.array_equal(outs[0], out) and abs(ss[0] - s) < 1e-12
+
+
+# ---------------------------------------------------------------- encoder-side filter selection
+
+def _png_from_stream(w, h, bd, ct, stream):
+    """Assemble a PNG around a filtered scanline stream (chunk.rs:17-96 layout: IHDR, one IDAT, IEND)."""
+    import zlib
+
+    def chunk(typ, body):
+        return struct.pack(">I", len(body)) + typ + body + struct.pack(">I", zlib.crc32(typ + body) & 0xFFFFFFFF)
+    ihdr = struct.pack(">IIBBBBB", w, h, bd, ct, 0, 0, 0)
+    return b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", ihdr) + chunk(b"IDAT", zlib.compress(bytes(stream), 1)) + chunk(b"IEND", b"")
+
+
+def test_filter_selection_round_trips(oracle):
+    """scanline_writer.rs:22-104 restated: the chosen filters decode back to the same pixels, both through
+    the oracle's own decoder and through PIL (spec Paeth)."""
+    import io
+    from PIL import Image
+    rng = np.random.default_rng(5)
+    for (w, h, ch, bd, ct) in ((61, 40, 4, 8, 6), (33, 17, 3, 8, 2), (50, 9, 1, 8, 0), (20, 11, 2, 16, 4)):
+        bpp, rowb = max(1, ch * bd // 8), (w * ch * bd + 7) // 8
+        base = smooth_rgba(rowb, h, seed=w)[..., 0]  # smooth bytes so that all five filters get chosen somewhere
+        px = (base + rng.integers(0, 3, size=base.shape)).astype(np.uint8)
+        stream, ft = oracle.filter_scanlines(px, h, rowb, bpp, 0)
+        d = oracle.png_decode(_png_from_stream(w, h, bd, ct, stream))
+        assert np.array_equal(d.pixels, px.reshape(-1))
+        if bd == 8:
+            im = np.asarray(Image.open(io.BytesIO(_png_from_stream(w, h, bd, ct, stream))))
+            assert np.array_equal(im.reshape(h, rowb), px)
+        # the winner really has the smallest byte sum (first minimum)
+        for y in range(h):
+            row = stream[y * (rowb + 1) + 1:(y + 1) * (rowb + 1)]
+            assert stream[y * (rowb + 1)] == ft[y] <= 4
+            if ft[y] == 0:
+                assert np.array_equal(row, px[y])
+
+
+def test_reference_encoder_round_trip_on_obama(oracle):
+    """encoder.rs:64-79 (`test_encode_round_trip`): decode(encode(decode(obama))) == decode(obama) holds in
+    the reference even with its `a + b + c` Paeth (scanline_writer.rs:8); the bug-for-bug mode of the oracle
+    must therefore round-trip obama through the spec decoder too."""
+    data = open(os.path.join(GOLDEN, "images", "obama.png"), "rb").read()
+    d = oracle.png_decode(data)
+    rowb = d.width * 3
+    for compat in (1, 0):
+        stream, ft = oracle.filter_scanlines(d.pixels, d.height, rowb, 3, compat)
+        back = oracle.png_decode(_png_from_stream(d.width, d.height, 8, 2, stream))
+        assert np.array_equal(back.pixels, d.pixels), compat
