@@ -268,7 +268,7 @@ def main():
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json, burst copy)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
-    # The step is ONE fused kernel (chain_fused_kernel<R,...>: front + blur + Sobel + SSIM moments) plus a
+    # The step is ONE fused kernel (chain_fused2_kernel<R,...>: front + blur + Sobel + SSIM moments) plus a
     # finalize launch of <10 us, so the kernel's launch duration is the CUDA-event step time measured above on
     # the library's own stream.  Algorithmic bytes: 4 B/px source read + 4 B/px result written.
     k_bytes = n * PX * 8.0
@@ -280,7 +280,7 @@ def main():
         ncu_traffic = prof["dram_bytes_per_pixel"] * n * PX
     except Exception:
         pass
-    roofline = {"bound": "hbm", "kernel": "chain_fused_kernel<R=%d> (front+blur+Sobel+SSIM, one pass)" % args.radius,
+    roofline = {"bound": "hbm", "kernel": "chain_fused2_kernel<R=%d> (front+blur+Sobel+SSIM, one pass)" % args.radius,
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic,
                 "peak_source": peak_src, "algorithmic_bytes_per_pixel": 8, "launch_pixels": n * PX,
                 "launch_ms": kms,
