@@ -288,6 +288,43 @@ norm_status norm_cuda_blur(norm_ctx *ctx, uint32_t radius, const norm_img *in, n
 norm_status norm_cuda_sobel(norm_ctx *ctx, const norm_img *in, norm_img *out);
 /* sharpen, image_shader.wgsl:120-129 */
 norm_status norm_cuda_sharpen(norm_ctx *ctx, uint32_t factor, const norm_img *in, norm_img *out);
+/* box_blur, image_shader.wgsl:105-118: 3x3 mean of all four channels.  Defined but never called
+ * in the reference (no FeatureUniform field selects it), so it is only reachable here. */
+norm_status norm_cuda_box_blur(norm_ctx *ctx, const norm_img *in, norm_img *out);
+
+/* ---- shape overlay, composite, crosshair ------------------------------- */
+
+/* shape_uniform.rs:3-10 */
+typedef struct NormShapeUniform {
+    uint32_t width, height;    /* window size == image size (app_state.rs:79) */
+    uint32_t num_circles;      /* <= NORM_MAX_CIRCLES (shape_uniform.rs:60) */
+    uint32_t selected_circle;  /* index of the selected circle, 0xFFFFFFFF = none */
+} NormShapeUniform;
+/* shape_uniform.rs:38-45: centre and radius in normalised window coordinates
+ * (x / width, y / height, radius / min(width, height); shape.rs:188-243) */
+typedef struct NormCircleData {
+    float x, y, radius, _padding;
+} NormCircleData;
+/* draw_uniform.rs:3-9.  circle_center_* / circle_radius are in pixels.  camera_view_proj belongs to
+ * the vertex stage (pan / zoom of the presented quad) and is not read here. */
+typedef struct NormDrawUniform {
+    uint32_t crosshair;
+    float circle_center_x, circle_center_y, circle_radius;
+    float camera_view_proj[4][4];
+} NormDrawUniform;
+#define NORM_MAX_CIRCLES 256u
+
+/* Replaces the shape render pass (shape_shader.wgsl:41-89: filled circles with smoothstep edge,
+ * outline on the selected one, blended in list order) and the tail of the image fragment shader
+ * (image_shader.wgsl:176-193: composite of the shape layer, then the crosshair disc) applied to
+ * every frame of `in`; the result goes to the headless RGBA8 buffer `out` (no window, swapchain or
+ * present).  circles: host array of shapes->num_circles entries.  draw may be NULL (no crosshair).
+ * The shape layer passes through an sRGB 8-bit render texture as in the reference (gpu_state.rs:
+ * 404-418); pixels that nothing touches keep their bytes.  NORM_E_DIM_MISMATCH unless
+ * shapes->width/height equal the image size; NORM_E_INVALID_ARG for more than NORM_MAX_CIRCLES.
+ * Texture-space operation: apply it before FlipX / FlipY, as the reference's vertex stage does. */
+norm_status norm_cuda_overlay(norm_ctx *ctx, const NormShapeUniform *shapes, const NormCircleData *circles,
+                              const NormDrawUniform *draw, const norm_img *in, norm_img *out);
 
 /* ---- SSIM --------------------------------------------------------------------------- */
 
@@ -339,6 +376,9 @@ norm_status norm_cuda_ssim_static(const void *a_dev, const void *b_dev, uint32_t
 norm_status norm_blur_taps(uint32_t radius, float *taps, int32_t *dmin);
 /* 256-entry front table: sRGB decode at load + gamma pass + unorm8 store. */
 norm_status norm_front_lut(uint32_t flags, uint32_t gamma, uint8_t lut[256]);
+/* sRGB tables of the shape render texture: eotf[k] = decoded value of code k; thresh[j] = linear
+ * value at which the encoder steps from code j-1 to code j (thresh[0] = 0). */
+norm_status norm_srgb_tables(float eotf[256], float thresh[256]);
 /* Row-band plan for one giant image over `nranks` GPUs: rank `rank` owns rows
  * [*row0, *row0 + *rows) and needs *halo_up / *halo_down source rows from its neighbours
  * for the enabled stencil stages of `f`. */

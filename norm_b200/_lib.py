@@ -48,6 +48,26 @@ class NormPngDesc(C.Structure):
     ]
 
 
+class NormShapeUniform(C.Structure):
+    """src/renderer/shape_uniform.rs:3-10"""
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("num_circles", C.c_uint32),
+                ("selected_circle", C.c_uint32)]
+
+
+class NormCircleData(C.Structure):
+    """src/renderer/shape_uniform.rs:38-45"""
+    _fields_ = [("x", C.c_float), ("y", C.c_float), ("radius", C.c_float), ("_padding", C.c_float)]
+
+
+class NormDrawUniform(C.Structure):
+    """src/renderer/draw_uniform.rs:3-9"""
+    _fields_ = [("crosshair", C.c_uint32), ("circle_center_x", C.c_float), ("circle_center_y", C.c_float),
+                ("circle_radius", C.c_float), ("camera_view_proj", (C.c_float * 4) * 4)]
+
+
+assert C.sizeof(NormShapeUniform) == 16 and C.sizeof(NormCircleData) == 16 and C.sizeof(NormDrawUniform) == 80
+NORM_MAX_CIRCLES = 256
+
 _vp, _u32, _i32, _sz = C.c_void_p, C.c_uint32, C.c_int32, C.c_size_t
 _fu = C.POINTER(NormFeatureUniform)
 _dp = C.POINTER(C.c_double)
@@ -96,12 +116,16 @@ PROTOTYPES = {
     "norm_cuda_blur": (_i32, [_vp, _u32, _vp, _vp]),
     "norm_cuda_sobel": (_i32, [_vp, _vp, _vp]),
     "norm_cuda_sharpen": (_i32, [_vp, _u32, _vp, _vp]),
+    "norm_cuda_box_blur": (_i32, [_vp, _vp, _vp]),
+    "norm_cuda_overlay": (_i32, [_vp, C.POINTER(NormShapeUniform), C.POINTER(NormCircleData),
+                                 C.POINTER(NormDrawUniform), _vp, _vp]),
     "norm_cuda_ssim": (_i32, [_vp, _vp, _vp, _dp]),
     "norm_cuda_ssim_moments": (_i32, [_vp, _vp, _vp, _dp]),
     "norm_ssim_from_moments": (C.c_double, [_dp, C.c_double]),
     "norm_cuda_ssim_static": (_i32, [_vp, _vp, _u32, _u32, _u32, _sz, _sz, _vp, _vp, _vp]),
     "norm_blur_taps": (_i32, [_u32, C.POINTER(C.c_float), C.POINTER(_i32)]),
     "norm_front_lut": (_i32, [_u32, _u32, C.POINTER(C.c_uint8)]),
+    "norm_srgb_tables": (_i32, [C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "norm_plan_band": (_i32, [_fu, _u32, _i32, _i32, C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_u32),
                               C.POINTER(_u32)]),
     "norm_plan_frames": (_i32, [_u32, _i32, _i32, C.POINTER(_u32), C.POINTER(_u32)]),

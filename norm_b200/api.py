@@ -9,6 +9,8 @@ error behaviour (INTEGRATION.md holds the Rust binding a maintainer would add):
   Texture          src/renderer/texture.rs:22-80
   EffectPipeline   src/renderer/effect_pipeline.rs:8-132
   compute_sim      src/png/ssim.rs:91-106
+  Circle / ShapeUniform / CircleData / DrawUniform
+                   src/renderer/shape.rs:188-243, shape_uniform.rs:3-60, draw_uniform.rs:3-56
 
 Everything that computes goes through libnorm_cuda.so; numpy is used only to hold host bytes.
 """
@@ -18,7 +20,8 @@ import numpy as np
 
 from . import _lib
 from ._lib import (NORM_CS_RAW, NORM_CS_REFERENCE, NORM_EXPAND_COMPAT, NORM_EXPAND_SPEC, NORM_OK,
-                   NormFeatureUniform, NormInflatedDesc, NormPngDesc)
+                   NORM_MAX_CIRCLES, NormCircleData, NormDrawUniform, NormFeatureUniform, NormInflatedDesc,
+                   NormPngDesc, NormShapeUniform)
 
 
 class NormError(RuntimeError):
@@ -77,6 +80,57 @@ class FeatureUniform:
         f = FeatureUniform(self.raw.width, self.raw.height, self.raw.gamma)
         C.memmove(C.byref(f.raw), C.byref(self.raw), C.sizeof(NormFeatureUniform))
         return f
+
+
+class Circle:
+    """src/renderer/shape.rs:188-243: centre + radius, either in pixel or in normalised window space."""
+
+    def __init__(self, center, radius):
+        self.center, self.radius = (np.float32(center[0]), np.float32(center[1])), np.float32(radius)
+
+    @classmethod
+    def from_pixel_space(cls, center, radius, window_dimension):
+        w, h = np.float32(window_dimension[0]), np.float32(window_dimension[1])
+        return cls((np.float32(center[0]) / w, np.float32(center[1]) / h), np.float32(radius) / min(w, h))
+
+    def in_normalized_space(self, window_dimension):
+        return Circle.from_pixel_space(self.center, self.radius, window_dimension)
+
+    def in_pixel_space(self, window_dimension):
+        w, h = np.float32(window_dimension[0]), np.float32(window_dimension[1])
+        return Circle((self.center[0] * w, self.center[1] * h), self.radius * min(w, h))
+
+    def translate(self, offset):
+        return Circle((self.center[0] + np.float32(offset[0]), self.center[1] + np.float32(offset[1])), self.radius)
+
+    def data(self):
+        """impl From<&Circle> for CircleData (shape_uniform.rs:47-58)"""
+        return NormCircleData(float(self.center[0]), float(self.center[1]), float(self.radius), 0.0)
+
+
+class ShapeUniform:
+    """src/renderer/shape_uniform.rs:3-34"""
+
+    def __init__(self, width, height):
+        self.raw = NormShapeUniform(width, height, 0, 0xFFFFFFFF)
+
+    def update_dimensions(self, width, height): self.raw.width, self.raw.height = width, height
+    def set_num_circles(self, count): self.raw.num_circles = count
+    def set_selected_circle(self, selected): self.raw.selected_circle = 0xFFFFFFFF if selected is None else selected
+
+
+class DrawUniform:
+    """src/renderer/draw_uniform.rs:3-56"""
+
+    def __init__(self):
+        self.raw = NormDrawUniform()
+        for i in range(4):
+            self.raw.camera_view_proj[i][i] = 1.0
+
+    def crosshair(self): return self.raw.crosshair == 1
+    def toggle_crosshair(self): self.raw.crosshair = int(not self.crosshair())
+    def set_circle_center(self, x, y): self.raw.circle_center_x, self.raw.circle_center_y = x, y
+    def set_circle_radius(self, radius): self.raw.circle_radius = radius
 
 
 class Png:
@@ -340,6 +394,19 @@ class Context:
     def sobel(self, src, dst): self._ok(self.lib.norm_cuda_sobel(self.h, src.handle, dst.handle))
     def sharpen(self, factor, src, dst): self._ok(self.lib.norm_cuda_sharpen(self.h, factor, src.handle, dst.handle))
 
+    def box_blur(self, src, dst): self._ok(self.lib.norm_cuda_box_blur(self.h, src.handle, dst.handle))
+
+    def overlay(self, src, dst, circles=(), selected=None, draw=None):
+        """Shape pass + composite + crosshair (shape_shader.wgsl:41-89, image_shader.wgsl:176-193).
+        circles: Circle objects in normalised space (as EditorState holds them); selected: index
+        or None (ShapeUniform::set_selected_circle); draw: DrawUniform or None."""
+        su = ShapeUniform(src.width, src.height)
+        su.set_num_circles(len(circles))
+        su.set_selected_circle(selected)
+        arr = (NormCircleData * max(len(circles), 1))(*[c.data() for c in circles])
+        self._ok(self.lib.norm_cuda_overlay(self.h, C.byref(su.raw), arr, C.byref(draw.raw) if draw else None,
+                                            src.handle, dst.handle))
+
     def ssim(self, a, b):
         s = np.zeros(a.frames, np.float64)
         self._ok(self.lib.norm_cuda_ssim(self.h, a.handle, b.handle, s.ctypes.data_as(C.POINTER(C.c_double))))
@@ -460,6 +527,12 @@ def blur_taps(radius):
     if st != NORM_OK:
         raise NormError(st, "blur radius outside 1..63")
     return taps, dmin.value
+
+
+def srgb_tables():
+    eotf, thresh = np.zeros(256, np.float32), np.zeros(256, np.float32)
+    _lib.load().norm_srgb_tables(eotf.ctypes.data_as(C.POINTER(C.c_float)), thresh.ctypes.data_as(C.POINTER(C.c_float)))
+    return eotf, thresh
 
 
 def front_lut(flags, gamma):

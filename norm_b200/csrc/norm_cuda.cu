@@ -19,6 +19,7 @@
 #include "chain2_kernels.cuh"
 #include "common.cuh"
 #include "filter_kernels.cuh"
+#include "overlay_kernels.cuh"
 #include "stage_kernels.cuh"
 #include "unfilter_kernels.cuh"
 
@@ -274,6 +275,22 @@ norm_status launch_sharpen(norm_ctx *ctx, cudaStream_t s, const ImgView &in, con
     sharpen_kernel<<<grid, 256, 0, s>>>(in, out, (int)factor, tx, ty);
     LAUNCH_CHECK(ctx);
     return NORM_OK;
+}
+
+norm_status launch_box_blur(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const ImgView &out) {
+    const uint32_t tx = (in.w + kStW - 1) / kStW, ty = (in.h + kStH - 1) / kStH;
+    const unsigned grid = grid_for(ctx, (size_t)tx * ty * in.frames, 8);
+    box_blur_kernel<<<grid, 256, 0, s>>>(in, out, tx, ty);
+    LAUNCH_CHECK(ctx);
+    return NORM_OK;
+}
+
+// sRGB encode thresholds / decode values of the shape render texture (host, double -> f32)
+void make_srgb_tables(float *eotf, float *thresh) {
+    for (int k = 0; k < 256; ++k) {
+        eotf[k] = (float)srgb_eotf((double)k / 255.0);
+        thresh[k] = k == 0 ? 0.0f : (float)srgb_eotf(((double)k - 0.5) / 255.0);
+    }
 }
 
 norm_status copy_view(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const ImgView &out) {
@@ -1302,6 +1319,52 @@ norm_status norm_cuda_sobel(norm_ctx *ctx, const norm_img *in, norm_img *out) {
     return NORM_OK;
 }
 
+norm_status norm_cuda_box_blur(norm_ctx *ctx, const norm_img *in, norm_img *out) {
+    NORM_TRY(bind(ctx));
+    NORM_TRY(check_pair(ctx, in, out, false));
+    NORM_TRY(launch_box_blur(ctx, ctx->main.stream, in->v, out->v));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    return NORM_OK;
+}
+
+norm_status norm_cuda_overlay(norm_ctx *ctx, const NormShapeUniform *shapes, const NormCircleData *circles,
+                              const NormDrawUniform *draw, const norm_img *in, norm_img *out) {
+    NORM_TRY(bind(ctx));
+    NORM_TRY(check_pair(ctx, in, out, false));
+    if (!shapes) return fail(ctx, NORM_E_INVALID_ARG, "shape uniform is NULL");
+    if (shapes->num_circles > NORM_MAX_CIRCLES)
+        return fail(ctx, NORM_E_INVALID_ARG, "num_circles exceeds NORM_MAX_CIRCLES (256, shape_uniform.rs:60)");
+    if (shapes->num_circles && !circles) return fail(ctx, NORM_E_INVALID_ARG, "circles is NULL");
+    if (shapes->width != in->v.w || shapes->height != in->v.h)
+        return fail(ctx, NORM_E_DIM_MISMATCH, "shape uniform width/height differ from the image");
+    static const SrgbTables tables = [] {
+        SrgbTables t;
+        make_srgb_tables(t.eotf, t.thresh);
+        return t;
+    }();
+    OverlayParams op{};
+    // shape_shader.wgsl:52-57: back to pixel coordinates, one f32 product each
+    const float W = (float)shapes->width, H = (float)shapes->height,
+                M = (float)std::min(shapes->width, shapes->height);
+    for (uint32_t i = 0; i < shapes->num_circles; ++i) {
+        op.cx[i] = circles[i].x * W;
+        op.cy[i] = circles[i].y * H;
+        op.rp[i] = circles[i].radius * M;
+    }
+    op.num_circles = shapes->num_circles;
+    op.selected = shapes->selected_circle;
+    if (draw && draw->crosshair == 1u) {
+        op.crosshair = 1;
+        op.mx = draw->circle_center_x, op.my = draw->circle_center_y, op.mr = draw->circle_radius;
+    }
+    const uint32_t tx = (in->v.w + kOvW - 1) / kOvW, ty = (in->v.h + kOvH - 1) / kOvH;
+    const unsigned grid = grid_for(ctx, (size_t)tx * ty * in->v.frames, 8);
+    overlay_kernel<<<grid, 256, 0, ctx->main.stream>>>(in->v, out->v, op, tables, tx, ty);
+    LAUNCH_CHECK(ctx);
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    return NORM_OK;
+}
+
 norm_status norm_cuda_sharpen(norm_ctx *ctx, uint32_t factor, const norm_img *in, norm_img *out) {
     NORM_TRY(bind(ctx));
     NORM_TRY(check_pair(ctx, in, out, false));
@@ -1435,6 +1498,12 @@ norm_status norm_blur_taps(uint32_t radius, float *taps, int32_t *dmin) {
     if (!taps || !dmin || make_taps(radius, t) != NORM_OK) return NORM_E_INVALID_ARG;
     std::memcpy(taps, t.t, radius * sizeof(float));
     *dmin = t.dmin;
+    return NORM_OK;
+}
+
+norm_status norm_srgb_tables(float eotf[256], float thresh[256]) {
+    if (!eotf || !thresh) return NORM_E_INVALID_ARG;
+    make_srgb_tables(eotf, thresh);
     return NORM_OK;
 }
 

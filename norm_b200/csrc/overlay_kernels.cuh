@@ -1,0 +1,169 @@
+// Shape overlay, composite and crosshair: the last arithmetic between the effect
+// output and the final pixel.  Follows shape_shader.wgsl:41-89 (circle fill with smoothstep AA,
+// selected-circle outline, sequential mix blending), the ALPHA_BLENDING store into the sRGB shape
+// texture (gpu_state.rs:321,404-418; cleared transparent, app_state.rs:589), and the composite +
+// crosshair of image_shader.wgsl:176-193.  Same fixed operation order as oracle_overlay().
+//
+// HBM-bound for the pixels nothing touches (16-byte load -> 16-byte store); every CTA first
+// culls the circle list against its tile so the per-pixel loop only walks circles that can
+// reach the tile (culling is conservative, so the result equals the full loop).
+#pragma once
+#include "common.cuh"
+
+namespace normk {
+
+constexpr int kMaxCircles = 256;              // shape_uniform.rs:60 MAX_CIRCLES
+constexpr int kOvW = 128, kOvH = 8;           // tile: 32 threads x 4 px wide, 8 rows
+
+struct OverlayParams {
+    float cx[kMaxCircles], cy[kMaxCircles], rp[kMaxCircles];  // pixel-space centre / radius
+    uint32_t num_circles, selected;
+    uint32_t crosshair;
+    float mx, my, mr;  // draw_uniform.rs: circle_center_x/y, circle_radius (pixels)
+};
+
+struct SrgbTables {
+    float eotf[256];    // decoded value of code k
+    float thresh[256];  // thresh[j]: encoder steps from code j-1 to j at this linear value
+};
+
+__device__ __forceinline__ float smoothstep_rn(float e0, float e1, float x) {
+    float t = __fdiv_rn(__fsub_rn(x, e0), __fsub_rn(e1, e0));
+    t = fminf(fmaxf(t, 0.0f), 1.0f);
+    return __fmul_rn(__fmul_rn(t, t), __fsub_rn(3.0f, __fmul_rn(2.0f, t)));
+}
+
+__device__ __forceinline__ float mix_rn(float a, float b, float t) {
+    return __fmaf_rn(b, t, __fmul_rn(a, __fsub_rn(1.0f, t)));
+}
+
+__device__ __forceinline__ uint32_t unorm8_rn(float v) {
+    v = fminf(fmaxf(v, 0.0f), 1.0f);
+    return (uint32_t)__float2int_rn(__fmul_rn(v, 255.0f));
+}
+
+__device__ __forceinline__ uint32_t srgb_code(const float *thresh, float v) {
+    uint32_t lo = 0, hi = 255;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        const uint32_t mid = (lo + hi + 1) >> 1;
+        if (v >= thresh[mid]) lo = mid;
+        else hi = mid - 1;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(256) overlay_kernel(ImgView in, ImgView out, const __grid_constant__ OverlayParams op,
+                                                      const __grid_constant__ SrgbTables tab, uint32_t tiles_x,
+                                                      uint32_t tiles_y) {
+    __shared__ float s_cx[kMaxCircles], s_cy[kMaxCircles], s_rp[kMaxCircles];
+    __shared__ uint16_t s_idx[kMaxCircles];
+    __shared__ uint32_t s_warp_cnt[8];
+    __shared__ float s_eotf[256], s_thresh[256];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    s_eotf[tid] = tab.eotf[tid];
+    s_thresh[tid] = tab.thresh[tid];
+    const uint32_t n = op.num_circles, selected = op.selected;
+    const bool cross = op.crosshair == 1u;
+    const float mx = op.mx, my = op.my, mr = op.mr;
+    const uint32_t tiles_per_frame = tiles_x * tiles_y;
+    const size_t total = (size_t)tiles_per_frame * in.frames;
+    for (size_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const uint32_t f = (uint32_t)(tile / tiles_per_frame);
+        const uint32_t tr = (uint32_t)(tile - (size_t)f * tiles_per_frame);
+        const int x0 = (int)(tr % tiles_x) * kOvW, y0 = (int)(tr / tiles_x) * kOvH;
+        __syncthreads();
+        // ---- cull: thread i looks at circle i; ordered compaction keeps the blending order
+        bool keep = false;
+        if ((uint32_t)tid < n) {
+            const float cx = op.cx[tid], cy = op.cy[tid], rp = op.rp[tid];
+            // distance from the centre to the tile's pixel-centre box, with 4 px of margin for
+            // the outline (3 px) and rounding
+            const float bx0 = (float)x0 + 0.5f, bx1 = (float)min(x0 + kOvW, (int)in.w) - 0.5f;
+            const float by0 = (float)y0 + 0.5f, by1 = (float)min(y0 + kOvH, (int)in.h) - 0.5f;
+            const float ddx = fmaxf(fmaxf(bx0 - cx, cx - bx1), 0.0f), ddy = fmaxf(fmaxf(by0 - cy, cy - by1), 0.0f);
+            const float dmin = sqrtf(ddx * ddx + ddy * ddy);
+            // NaN parameters never satisfy d <= rp, so dropping them here changes nothing
+            keep = dmin <= rp + 4.0f;
+        }
+        const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) s_warp_cnt[warp] = __popc(bal);
+        __syncthreads();
+        uint32_t base = 0, cnt = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+            if (w < warp) base += s_warp_cnt[w];
+            cnt += s_warp_cnt[w];
+        }
+        if (keep) {
+            const uint32_t pos = base + __popc(bal & ((1u << lane) - 1u));
+            s_idx[pos] = (uint16_t)tid;
+            s_cx[pos] = op.cx[tid], s_cy[pos] = op.cy[tid], s_rp[pos] = op.rp[tid];
+        }
+        __syncthreads();
+
+        const int ry = tid >> 5, cxq = tid & 31;
+        const int y = y0 + ry, x = x0 + 4 * cxq;
+        if (y >= (int)in.h || x >= (int)in.w) continue;
+        const uint4 src = ldg_stream(reinterpret_cast<const uint4 *>(row_ptr(in, f, y)) + (x >> 2));
+        uint32_t px[4] = {src.x, src.y, src.z, src.w};
+        const float py = __fadd_rn((float)y, 0.5f);
+        // tile-level early out: no circle reaches the tile and the crosshair disc cannot either
+        bool tile_cross = cross;
+        if (cross) {
+            const float bx0 = (float)x0 + 0.5f, bx1 = (float)min(x0 + kOvW, (int)in.w) - 0.5f;
+            const float by0 = (float)y0 + 0.5f, by1 = (float)min(y0 + kOvH, (int)in.h) - 0.5f;
+            const float ddx = fmaxf(fmaxf(bx0 - mx, mx - bx1), 0.0f), ddy = fmaxf(fmaxf(by0 - my, my - by1), 0.0f);
+            tile_cross = sqrtf(ddx * ddx + ddy * ddy) <= mr + 1.0f;
+        }
+        if (cnt != 0 || tile_cross) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (x + j >= (int)in.w) break;
+                const float pxc = __fadd_rn((float)(x + j), 0.5f);
+                float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f, c3 = 0.0f;
+                for (uint32_t k = 0; k < cnt; ++k) {
+                    const float rp = s_rp[k];
+                    const float dx = __fsub_rn(pxc, s_cx[k]), dy = __fsub_rn(py, s_cy[k]);
+                    const float d = __fsqrt_rn(__fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
+                    if (d <= rp) {
+                        const float a = __fsub_rn(1.0f, smoothstep_rn(__fsub_rn(rp, 1.0f), rp, d));
+                        c0 = mix_rn(c0, 0.0f, a), c1 = mix_rn(c1, 1.0f, a);
+                        c2 = mix_rn(c2, 1.0f, a), c3 = mix_rn(c3, a, a);
+                    }
+                    if (s_idx[k] == selected) {
+                        const float od = fabsf(__fsub_rn(d, rp));
+                        if (od <= 3.0f) {
+                            const float a = __fsub_rn(1.0f, smoothstep_rn(0.0f, 3.0f, od));
+                            c0 = mix_rn(c0, 1.0f, a), c1 = mix_rn(c1, 1.0f, a);
+                            c2 = mix_rn(c2, 0.0f, a), c3 = mix_rn(c3, a, a);
+                        }
+                    }
+                }
+                const uint32_t ca = unorm8_rn(c3);
+                bool hit = false;
+                if (tile_cross) {
+                    const float dx = __fsub_rn(pxc, mx), dy = __fsub_rn(py, my);
+                    hit = __fsqrt_rn(__fmaf_rn(dy, dy, __fmul_rn(dx, dx))) < mr;
+                }
+                if (ca == 0 && !hit) continue;
+                float p[4];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) p[c] = __fdiv_rn(byte_f(px[j], c), 255.0f);
+                if (ca > 0) {
+                    const float sa = __fdiv_rn((float)ca, 255.0f);
+                    p[0] = mix_rn(p[0], s_eotf[srgb_code(s_thresh, __fmul_rn(c0, c3))], sa);
+                    p[1] = mix_rn(p[1], s_eotf[srgb_code(s_thresh, __fmul_rn(c1, c3))], sa);
+                    p[2] = mix_rn(p[2], s_eotf[srgb_code(s_thresh, __fmul_rn(c2, c3))], sa);
+                    p[3] = mix_rn(p[3], sa, sa);
+                }
+                if (hit) p[0] = 0.0f, p[1] = 1.0f, p[2] = 1.0f;
+                px[j] = pack_rgba(unorm8_rn(p[0]), unorm8_rn(p[1]), unorm8_rn(p[2]), unorm8_rn(p[3]));
+            }
+        }
+        stg_stream(reinterpret_cast<uint4 *>(const_cast<uint8_t *>(row_ptr(out, f, y))) + (x >> 2),
+                   make_uint4(px[0], px[1], px[2], px[3]));
+    }
+}
+
+}  // namespace normk

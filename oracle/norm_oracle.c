@@ -810,6 +810,135 @@ void oracle_sharpen_r(const uint8_t *in, uint32_t w, uint32_t h, uint32_t factor
 }
 
 /* ------------------------------------------------------------------------------------ */
+/* Box blur (dead code in the reference, image_shader.wgsl:105-118)                     */
+/* ------------------------------------------------------------------------------------ */
+
+/* 3x3 mean of all four channels, ClampToEdge.  S-form: the nine raw bytes sum exactly in
+ * integers, one f32 division by 9, round half even. */
+void oracle_box_blur_s(const uint8_t *in, uint32_t w, uint32_t h, uint8_t *out) {
+#pragma omp parallel for schedule(static)
+    for (int y = 0; y < (int)h; ++y)
+        for (int x = 0; x < (int)w; ++x)
+            for (int c = 0; c < 4; ++c) {
+                int sum = 0;
+                for (int dx = -1; dx <= 1; ++dx)
+                    for (int dy = -1; dy <= 1; ++dy)
+                        sum += in[((size_t)clampi(y + dy, 0, (int)h - 1) * w + clampi(x + dx, 0, (int)w - 1)) * 4 + c];
+                out[((size_t)y * w + x) * 4 + c] = quant_raw((float)sum / 9.0f);
+            }
+}
+
+/* Literal order: dx outer, dy inner, unit-scale f32 accumulation, divide by the f32 count. */
+void oracle_box_blur_r(const uint8_t *in, uint32_t w, uint32_t h, uint8_t *out) {
+    for (int y = 0; y < (int)h; ++y)
+        for (int x = 0; x < (int)w; ++x)
+            for (int c = 0; c < 4; ++c) {
+                float acc = 0.0f, ct = 0.0f;
+                for (int dx = -1; dx <= 1; ++dx)
+                    for (int dy = -1; dy <= 1; ++dy) {
+                        acc += (float)in[((size_t)clampi(y + dy, 0, (int)h - 1) * w + clampi(x + dx, 0, (int)w - 1)) * 4 + c] / 255.0f;
+                        ct += 1.0f;
+                    }
+                out[((size_t)y * w + x) * 4 + c] = unorm8(acc / ct);
+            }
+}
+
+/* ------------------------------------------------------------------------------------ */
+/* Shape overlay + composite + crosshair                                                */
+/* ------------------------------------------------------------------------------------ */
+
+/* sRGB tables for the shape render texture, which has the surface's sRGB format
+ * (gpu_state.rs:404-418): eotf[k] = decoded value of code k; thresh[j] (j = 1..255) = the
+ * linear value at which the encoder steps from code j-1 to code j, i.e. EOTF((j-0.5)/255).
+ * thresh[0] = 0.  Both evaluated in double, rounded once to f32. */
+void oracle_srgb_tables(float eotf[256], float thresh[256]) {
+    for (int k = 0; k < 256; ++k) {
+        eotf[k] = (float)srgb_eotf((double)k / 255.0);
+        thresh[k] = k == 0 ? 0.0f : (float)srgb_eotf(((double)k - 0.5) / 255.0);
+    }
+}
+
+static inline unsigned srgb_code(const float thresh[256], float v) {
+    unsigned lo = 0, hi = 255;
+    while (lo < hi) {
+        const unsigned mid = (lo + hi + 1) >> 1;
+        if (v >= thresh[mid]) lo = mid;
+        else hi = mid - 1;
+    }
+    return lo;
+}
+
+static inline float smoothstep_f(float e0, float e1, float x) {
+    float t = (x - e0) / (e1 - e0);
+    t = fminf(fmaxf(t, 0.0f), 1.0f);
+    return (t * t) * (3.0f - 2.0f * t);
+}
+
+/* WGSL mix(a, b, t) = a (1 - t) + b t, the second product fused into the sum */
+static inline float mix_f(float a, float b, float t) { return fmaf(b, t, a * (1.0f - t)); }
+
+/* shape_shader.wgsl:41-89 (fragment of the shape pass) -> ALPHA_BLENDING over a transparent
+ * clear (gpu_state.rs:321, app_state.rs:589) -> store in the sRGB render texture -> sampled at
+ * the texel centre and composited in image_shader.wgsl:176-193, then the crosshair disc.
+ * Pixel (x, y) has pixel_coords (x + 0.5, y + 0.5).  A pixel that no circle, outline or
+ * crosshair touches keeps its bytes.  Camera transform (vertex stage) is not modelled. */
+int oracle_overlay(const uint8_t *in, uint32_t w, uint32_t h, const oracle_shape_uniform *su,
+                   const oracle_circle *circles, const oracle_draw_uniform *du, uint8_t *out) {
+    if (!in || !out || !su || (su->num_circles && !circles)) return ORACLE_E_INVALID;
+    if (su->width != w || su->height != h || su->num_circles > 256) return ORACLE_E_INVALID;
+    float eotf[256], thresh[256];
+    oracle_srgb_tables(eotf, thresh);
+    const float W = (float)w, H = (float)h, M = (float)(w < h ? w : h);
+#pragma omp parallel for schedule(static)
+    for (int y = 0; y < (int)h; ++y)
+        for (int x = 0; x < (int)w; ++x) {
+            const float px = (float)x + 0.5f, py = (float)y + 0.5f;
+            float col[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+            for (uint32_t i = 0; i < su->num_circles; ++i) {
+                const float cx = circles[i].x * W, cy = circles[i].y * H, rp = circles[i].radius * M;
+                const float dx = px - cx, dy = py - cy;
+                const float d = sqrtf(fmaf(dy, dy, dx * dx));
+                if (d <= rp) {
+                    const float a = 1.0f - smoothstep_f(rp - 1.0f, rp, d);
+                    col[0] = mix_f(col[0], 0.0f, a), col[1] = mix_f(col[1], 1.0f, a);
+                    col[2] = mix_f(col[2], 1.0f, a), col[3] = mix_f(col[3], a, a);
+                }
+                if (i == su->selected_circle) {
+                    const float od = fabsf(d - rp);
+                    if (od <= 3.0f) {
+                        const float a = 1.0f - smoothstep_f(0.0f, 3.0f, od);
+                        col[0] = mix_f(col[0], 1.0f, a), col[1] = mix_f(col[1], 1.0f, a);
+                        col[2] = mix_f(col[2], 0.0f, a), col[3] = mix_f(col[3], a, a);
+                    }
+                }
+            }
+            const uint8_t *s = in + ((size_t)y * w + x) * 4;
+            uint8_t *o = out + ((size_t)y * w + x) * 4;
+            /* render-target store: blend (rgb * a, a), sRGB-encode rgb, unorm8 alpha */
+            const unsigned ca = unorm8(col[3]);
+            int hit = 0;
+            if (du && du->crosshair == 1u) {
+                const float dx = px - du->circle_center_x, dy = py - du->circle_center_y;
+                hit = sqrtf(fmaf(dy, dy, dx * dx)) < du->circle_radius;
+            }
+            if (ca == 0 && !hit) {
+                memcpy(o, s, 4);
+                continue;
+            }
+            float p[4];
+            for (int c = 0; c < 4; ++c) p[c] = (float)s[c] / 255.0f;
+            if (ca > 0) {
+                const float sa = (float)ca / 255.0f;
+                for (int c = 0; c < 3; ++c) p[c] = mix_f(p[c], eotf[srgb_code(thresh, col[c] * col[3])], sa);
+                p[3] = mix_f(p[3], sa, sa);
+            }
+            if (hit) p[0] = 0.0f, p[1] = 1.0f, p[2] = 1.0f;
+            for (int c = 0; c < 4; ++c) o[c] = unorm8(p[c]);
+        }
+    return ORACLE_OK;
+}
+
+/* ------------------------------------------------------------------------------------ */
 /* SSIM                                                                                 */
 /* ------------------------------------------------------------------------------------ */
 

@@ -87,6 +87,26 @@ void oracle_sobel_r(const uint8_t *in, uint32_t w, uint32_t h, uint8_t *out);
 void oracle_sharpen_s(const uint8_t *in, uint32_t w, uint32_t h, uint32_t factor, uint8_t *out);
 void oracle_sharpen_r(const uint8_t *in, uint32_t w, uint32_t h, uint32_t factor, uint8_t *out);
 
+/* image_shader.wgsl:105-118 (dead code in the reference: defined, never called) */
+void oracle_box_blur_s(const uint8_t *in, uint32_t w, uint32_t h, uint8_t *out);
+void oracle_box_blur_r(const uint8_t *in, uint32_t w, uint32_t h, uint8_t *out);
+
+/* Shape overlay (shape_shader.wgsl:41-89), composite and crosshair (image_shader.wgsl:176-193).
+ * Structs are field-for-field shape_uniform.rs:3-10, :38-45 and draw_uniform.rs:3-9.
+ * Parity unpinned: the reference has no test for it and its render-target format and
+ * interpolated tex_coords are driver-defined; this is the restatement with exact pixel centres
+ * and an sRGB render texture. */
+typedef struct { uint32_t width, height, num_circles, selected_circle; } oracle_shape_uniform;
+typedef struct { float x, y, radius, pad; } oracle_circle;
+typedef struct {
+    uint32_t crosshair;
+    float circle_center_x, circle_center_y, circle_radius;
+    float camera_view_proj[4][4];
+} oracle_draw_uniform;
+void oracle_srgb_tables(float eotf[256], float thresh[256]);
+int oracle_overlay(const uint8_t *in, uint32_t w, uint32_t h, const oracle_shape_uniform *su,
+                   const oracle_circle *circles, const oracle_draw_uniform *du, uint8_t *out);
+
 /* src/png/ssim.rs:9-184 on two RGBA8 buffers (RGBA luma branch, ssim.rs:65-81).
  * moments = {sum x, sum y, sum x^2, sum y^2, sum x*y} over f32 lumas, accumulated in f64. */
 void oracle_ssim_moments(const uint8_t *a, const uint8_t *b, size_t npix, double m[5]);

@@ -43,6 +43,20 @@ class FeatureUniform(C.Structure):
 assert C.sizeof(FeatureUniform) == 112
 
 
+class ShapeUniform(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("num_circles", C.c_uint32),
+                ("selected_circle", C.c_uint32)]
+
+
+class CircleData(C.Structure):
+    _fields_ = [("x", C.c_float), ("y", C.c_float), ("radius", C.c_float), ("pad", C.c_float)]
+
+
+class DrawUniform(C.Structure):
+    _fields_ = [("crosshair", C.c_uint32), ("circle_center_x", C.c_float), ("circle_center_y", C.c_float),
+                ("circle_radius", C.c_float), ("camera_view_proj", (C.c_float * 4) * 4)]
+
+
 def make_uniform(w, h, gamma=0, grayscale=0, invert=0, blur=0, blur_radius=21, sharpen=0,
                  sharpen_factor=16, edge_detect=0):
     f = FeatureUniform()
@@ -92,6 +106,13 @@ def lib():
         for n in ("oracle_sobel_s", "oracle_sobel_r"):
             getattr(L, n).argtypes = [u8p, C.c_uint32, C.c_uint32, u8p]
             getattr(L, n).restype = None
+        for n in ("oracle_box_blur_s", "oracle_box_blur_r"):
+            getattr(L, n).argtypes = [u8p, C.c_uint32, C.c_uint32, u8p]
+            getattr(L, n).restype = None
+        L.oracle_srgb_tables.argtypes = [f32p, f32p]
+        L.oracle_srgb_tables.restype = None
+        L.oracle_overlay.argtypes = [u8p, C.c_uint32, C.c_uint32, C.POINTER(ShapeUniform), C.POINTER(CircleData),
+                                     C.POINTER(DrawUniform), u8p]
         for n in ("oracle_sharpen_s", "oracle_sharpen_r"):
             getattr(L, n).argtypes = [u8p, C.c_uint32, C.c_uint32, C.c_uint32, u8p]
             getattr(L, n).restype = None
@@ -254,6 +275,35 @@ def sharpen_s(img, factor):
 
 def sharpen_r(img, factor):
     return _stage(lib().oracle_sharpen_r, img, factor)
+
+
+def box_blur_s(img):
+    return _stage(lib().oracle_box_blur_s, img)
+
+
+def box_blur_r(img):
+    return _stage(lib().oracle_box_blur_r, img)
+
+
+def srgb_tables():
+    e, t = np.zeros(256, np.float32), np.zeros(256, np.float32)
+    lib().oracle_srgb_tables(e.ctypes.data_as(C.POINTER(C.c_float)), t.ctypes.data_as(C.POINTER(C.c_float)))
+    return e, t
+
+
+def overlay(img, circles=(), selected=None, crosshair=None):
+    """circles: (x, y, radius) in normalised space; crosshair: (cx, cy, radius) in pixels or None."""
+    img = _img(img)
+    out = np.empty_like(img)
+    su = ShapeUniform(img.shape[1], img.shape[0], len(circles), 0xFFFFFFFF if selected is None else selected)
+    arr = (CircleData * max(len(circles), 1))(*[CircleData(x, y, r, 0.0) for x, y, r in circles])
+    du = DrawUniform()
+    if crosshair is not None:
+        du.crosshair, du.circle_center_x, du.circle_center_y, du.circle_radius = 1, *crosshair
+    rc = lib().oracle_overlay(_u8(img), img.shape[1], img.shape[0], C.byref(su), arr, C.byref(du), _u8(out))
+    if rc != OK:
+        raise ValueError(f"oracle rc={rc}")
+    return out
 
 
 def ssim_moments(a, b):

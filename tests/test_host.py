@@ -99,3 +99,31 @@ def test_create_fails_loudly_without_gpu():
     with pytest.raises(nb.NormError) as e:
         nb.Context(0)
     assert e.value.status == nb._lib.NORM_E_CUDA and "no CPU fallback" in str(e.value)
+
+
+def test_shape_structs_and_srgb_tables(oracle):
+    """shape_uniform.rs / draw_uniform.rs layouts and the host-side sRGB tables of the overlay."""
+    import ctypes as C
+    from norm_b200 import _lib, api
+    assert C.sizeof(_lib.NormShapeUniform) == 16 and C.sizeof(_lib.NormCircleData) == 16
+    assert C.sizeof(_lib.NormDrawUniform) == 80 and _lib.NormDrawUniform.camera_view_proj.offset == 16
+    su = api.ShapeUniform(640, 480)
+    assert su.raw.selected_circle == 0xFFFFFFFF and su.raw.num_circles == 0
+    su.set_selected_circle(3), su.set_num_circles(7), su.update_dimensions(10, 20)
+    assert (su.raw.width, su.raw.height, su.raw.num_circles, su.raw.selected_circle) == (10, 20, 7, 3)
+    su.set_selected_circle(None)
+    assert su.raw.selected_circle == 0xFFFFFFFF
+    # Circle round trip pixel <-> normalised space (shape.rs:188-243)
+    c = api.Circle.from_pixel_space((320.0, 120.0), 48.0, (640.0, 480.0))
+    assert c.center == (0.5, 0.25) and c.radius == np.float32(0.1)
+    p = c.in_pixel_space((640.0, 480.0))
+    assert p.center == (320.0, 120.0) and abs(p.radius - 48.0) < 1e-4
+    d = c.data()
+    assert (d.x, d.y, d._padding) == (0.5, 0.25, 0.0)
+    du = api.DrawUniform()
+    assert not du.crosshair() and du.raw.camera_view_proj[2][2] == 1.0
+    du.toggle_crosshair()
+    assert du.crosshair()
+    e, t = api.srgb_tables()
+    oe, ot = oracle.srgb_tables()
+    assert (e == oe).all() and (t == ot).all()

@@ -369,3 +369,100 @@ def test_reference_encoder_round_trip_on_obama(oracle):
         stream, ft = oracle.filter_scanlines(d.pixels, d.height, rowb, 3, compat)
         back = oracle.png_decode(_png_from_stream(d.width, d.height, 8, 2, stream))
         assert np.array_equal(back.pixels, d.pixels), compat
+
+
+# ---- box blur and shape overlay -------------------------------------
+
+def test_box_blur_s_vs_r_and_numpy(oracle):
+    img = splitmix_rgba(53, 31, seed=5)
+    s, r = oracle.box_blur_s(img), oracle.box_blur_r(img)
+    assert np.abs(s.astype(int) - r.astype(int)).max() <= 1
+    pad = np.pad(img.astype(np.int64), ((1, 1), (1, 1), (0, 0)), mode="edge")
+    acc = sum(pad[1 + dy:1 + dy + 31, 1 + dx:1 + dx + 53] for dy in (-1, 0, 1) for dx in (-1, 0, 1))
+    ref = np.rint(acc / 9.0)  # no sum/9 lands on .5, so the rounding mode does not matter
+    assert np.abs(s.astype(int) - ref).max() <= 0
+    flat = np.full((9, 9, 4), 77, np.uint8)
+    assert (oracle.box_blur_s(flat) == flat).all()
+
+
+def _overlay_numpy(oracle, img, circles, selected, crosshair):
+    """Vectorised f32 restatement of shape_shader.wgsl:41-89 + image_shader.wgsl:176-193 (no fma)."""
+    f = np.float32
+    h, w = img.shape[:2]
+    eotf, thresh = oracle.srgb_tables()
+    px = (np.arange(w, dtype=f) + f(0.5))[None, :].repeat(h, 0)
+    py = (np.arange(h, dtype=f) + f(0.5))[:, None].repeat(w, 1)
+    col = np.zeros((h, w, 4), f)
+
+    def smooth(e0, e1, x):
+        t = np.clip((x - e0) / (e1 - e0), f(0), f(1))
+        return t * t * (f(3) - f(2) * t)
+
+    def mix(a, b, t):
+        return a * (f(1) - t) + b * t
+
+    for i, (cx, cy, r) in enumerate(circles):
+        cxp, cyp, rp = f(cx) * f(w), f(cy) * f(h), f(r) * f(min(w, h))
+        d = np.sqrt((px - cxp) ** 2 + (py - cyp) ** 2, dtype=f)
+        inside = d <= rp
+        a = np.where(inside, f(1) - smooth(rp - f(1), rp, d), f(0)).astype(f)
+        for c, v in enumerate((f(0), f(1), f(1))):
+            col[..., c] = np.where(inside, mix(col[..., c], v, a), col[..., c])
+        col[..., 3] = np.where(inside, mix(col[..., 3], a, a), col[..., 3])
+        if selected == i:
+            od = np.abs(d - rp)
+            near = od <= f(3)
+            a = np.where(near, f(1) - smooth(f(0), f(3), od), f(0)).astype(f)
+            for c, v in enumerate((f(1), f(1), f(0))):
+                col[..., c] = np.where(near, mix(col[..., c], v, a), col[..., c])
+            col[..., 3] = np.where(near, mix(col[..., 3], a, a), col[..., 3])
+    ca = np.rint(np.clip(col[..., 3], 0, 1) * f(255)).astype(np.int64)
+    code = np.searchsorted(thresh[1:], (col[..., :3] * col[..., 3:4]).astype(f), side="right")
+    sh = eotf[code]
+    p = img.astype(f) / f(255)
+    sa = (ca.astype(f) / f(255))[..., None]
+    blended = np.concatenate([mix(p[..., :3], sh, sa), mix(p[..., 3:], sa, sa)], axis=2)
+    p = np.where((ca > 0)[..., None], blended, p)
+    hit = np.zeros((h, w), bool)
+    if crosshair is not None:
+        hit = np.sqrt((px - f(crosshair[0])) ** 2 + (py - f(crosshair[1])) ** 2, dtype=f) < f(crosshair[2])
+        p[hit, 0], p[hit, 1], p[hit, 2] = 0, 1, 1
+    out = np.rint(np.clip(p, 0, 1) * f(255)).astype(np.uint8)
+    untouched = (ca == 0) & ~hit
+    out[untouched] = img[untouched]
+    return out
+
+
+def test_overlay_against_numpy_and_properties(oracle):
+    img = splitmix_rgba(160, 120, seed=9)
+    circles = [(0.5, 0.5, 0.2), (0.3, 0.4, 0.1), (0.9, 0.95, 0.15), (0.55, 0.5, 0.05)]
+    out = oracle.overlay(img, circles, selected=1, crosshair=(20.0, 100.0, 6.5))
+    ref = _overlay_numpy(oracle, img, circles, 1, (20.0, 100.0, 6.5))
+    d = np.abs(out.astype(int) - ref.astype(int))
+    assert d.max() <= 1 and (d > 0).mean() < 0.01  # fma vs separate rounding only
+    # interior of a filled circle is opaque cyan with alpha 255; far away nothing changes
+    assert tuple(out[60, 80]) == (0, 255, 255, 255)
+    assert (out[0:10, 0:10] == img[0:10, 0:10]).all()
+    # crosshair disc sets rgb = (0, 1, 1) and keeps alpha
+    assert tuple(out[100, 20][:3]) == (0, 255, 255) and out[100, 20][3] == img[100, 20][3]
+    # the selected circle gets a yellow ring at its radius: r = 0.1 * 120 = 12 px around (48, 48)
+    ring = out[48, 48 + 12]
+    assert ring[0] > 200 and ring[1] > 200 and ring[2] < 60
+    # no circles, no crosshair: identity
+    assert (oracle.overlay(img) == img).all()
+    # blending is in list order: the later small circle lies inside the first one, result unchanged cyan
+    assert tuple(out[60, 88]) == (0, 255, 255, 255)
+
+
+def test_overlay_rejects_bad_arguments(oracle):
+    img = splitmix_rgba(8, 8, seed=1)
+    with pytest.raises(ValueError):
+        oracle.overlay(img, [(0.5, 0.5, 0.1)] * 257)
+
+
+def test_srgb_tables(oracle):
+    eotf, thresh = oracle.srgb_tables()
+    assert eotf[0] == 0 and eotf[255] == 1 and (np.diff(eotf) > 0).all() and (np.diff(thresh[1:]) > 0).all()
+    # every code decodes to a value that encodes back to itself
+    code = np.searchsorted(thresh[1:], eotf, side="right")
+    assert (code == np.arange(256)).all()
