@@ -195,6 +195,14 @@ norm_status norm_cuda_unfilter(norm_ctx *ctx, const NormInflatedDesc *inflated, 
 norm_status norm_cuda_unfilter_expand_rgba8(norm_ctx *ctx, const NormInflatedDesc *inflated, const uint8_t *plte,
                                             int32_t n_plte, const uint8_t *trns, int32_t n_trns, int32_t mode,
                                             norm_img *out, uint32_t frame);
+/* Batch form: n streams of identical geometry (same width, height, bit depth, colour type and
+ * interlace flag -- the frames of a sequence), image i expanded into frame frame0 + i of `out`.
+ * One CTA per (image, Adam7 pass) runs the wavefront, so a batch scales over the SMs where a single
+ * image cannot.  Uses n * (stream + unfiltered) bytes of scratch.  The reference decodes one file
+ * at a time (decoder.rs:29-113); this is the same call made n times. */
+norm_status norm_cuda_unfilter_expand_rgba8_batch(norm_ctx *ctx, const NormInflatedDesc *inflated, uint32_t n,
+                                                  const uint8_t *plte, int32_t n_plte, const uint8_t *trns,
+                                                  int32_t n_trns, int32_t mode, norm_img *out, uint32_t frame0);
 
 /* ---- scanline filtering for the encoder (the step after the path) ---------- */
 

@@ -99,6 +99,8 @@ PROTOTYPES = {
     "norm_cuda_expand_rgba8_host": (_i32, [_vp, C.POINTER(NormPngDesc), _i32, _vp]),
     "norm_cuda_unfilter": (_i32, [_vp, C.POINTER(NormInflatedDesc), _vp]),
     "norm_cuda_unfilter_expand_rgba8": (_i32, [_vp, C.POINTER(NormInflatedDesc), _vp, _i32, _vp, _i32, _i32, _vp, _u32]),
+    "norm_cuda_unfilter_expand_rgba8_batch": (_i32, [_vp, C.POINTER(NormInflatedDesc), _u32, _vp, _i32, _vp, _i32, _i32,
+                                                     _vp, _u32]),
     "norm_cuda_filter_scanlines": (_i32, [_vp, _u32, _u32, C.c_uint8, C.c_uint8, _vp, _i32, _vp, _vp]),
     "norm_cuda_filter_image": (_i32, [_vp, _vp, _u32, _i32, _vp, _vp]),
     "norm_cuda_effects": (_i32, [_vp, _fu, _u32, _vp, _vp]),

@@ -315,6 +315,17 @@ class Context:
             self.h, C.byref(d), pl.ctypes.data if pl is not None else None, pl.size // 3 if pl is not None else 0,
             tr.ctypes.data if tr is not None else None, tr.size if tr is not None else 0, mode, out.handle, frame))
 
+    def unfilter_expand_batch(self, width, height, bit_depth, color_type, interlace, streams, mode, out, frame0=0,
+                              plte=None, trns=None):
+        """streams: inflated IDAT streams of identical geometry; stream i -> frame frame0 + i of out."""
+        pairs = [self._inflated(width, height, bit_depth, color_type, interlace, st) for st in streams]
+        arr = (NormInflatedDesc * max(len(pairs), 1))(*[d for d, _ in pairs])
+        pl = None if plte is None or len(plte) == 0 else np.ascontiguousarray(plte, np.uint8)
+        tr = None if trns is None or len(trns) == 0 else np.ascontiguousarray(trns, np.uint8)
+        self._ok(self.lib.norm_cuda_unfilter_expand_rgba8_batch(
+            self.h, arr, len(pairs), pl.ctypes.data if pl is not None else None, pl.size // 3 if pl is not None else 0,
+            tr.ctypes.data if tr is not None else None, tr.size if tr is not None else 0, mode, out.handle, frame0))
+
     # -- encoder-side scanline filtering (ScanlineWriter::write on the GPU)
     def filter_scanlines(self, width, height, bit_depth, color_type, pixel_buffer, paeth_compat=0):
         """pixel_buffer -> (stream of `filter byte + filtered row`, chosen filter per row)."""

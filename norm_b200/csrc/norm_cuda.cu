@@ -965,12 +965,15 @@ static void adam7_sizes(uint32_t w, uint32_t h, uint32_t pw[7], uint32_t ph[7]) 
     }
 }
 
-// Uploads the inflated stream and undoes the scanline filters (and Adam7) on the GPU.  The raster
-// pixel_buffer is left in device memory: *dev_out points at it, *pitch_out is its row stride
-// (row_bytes for interlaced images, a 16-byte-aligned pitch otherwise).
-static norm_status unfilter_to_device(norm_ctx *ctx, const NormInflatedDesc *d, const uint8_t **dev_out,
-                                      size_t *pitch_out, size_t *row_bytes_out) {
-    if (!d || !d->data) return fail(ctx, NORM_E_INVALID_ARG, "inflated descriptor / data is NULL");
+// Uploads n inflated streams of identical geometry and undoes the scanline filters (and Adam7) on
+// the GPU: one CTA per (image, pass) runs the wavefront, so a batch fills the machine where a single
+// image occupies one SM.  The raster pixel_buffers are left in device memory: *dev_out points at
+// image 0, *pitch_out is the row stride (row_bytes for interlaced images, a 16-byte-aligned pitch
+// otherwise) and image i starts *img_stride_out bytes after image i-1.
+static norm_status unfilter_to_device(norm_ctx *ctx, const NormInflatedDesc *descs, uint32_t n, const uint8_t **dev_out,
+                                      size_t *pitch_out, size_t *row_bytes_out, size_t *img_stride_out) {
+    if (!descs || n == 0) return fail(ctx, NORM_E_INVALID_ARG, "inflated descriptor is NULL / empty batch");
+    const NormInflatedDesc *d = &descs[0];
     const int ct = d->color_type, bd = d->bit_depth;
     if (!channels_of(ct) || !valid_depth(ct, bd)) return fail(ctx, NORM_E_INVALID_ARG, "invalid colour type / bit depth");
     if (d->width == 0 || d->height == 0 || d->interlace > 1) return fail(ctx, NORM_E_INVALID_ARG, "bad dimensions / interlace");
@@ -987,29 +990,42 @@ static norm_status unfilter_to_device(norm_ctx *ctx, const NormInflatedDesc *d, 
             pass_bytes += (size_t)ph[p] * align_up(rowb(pw[p]), 16);
             ft_bytes += align_up(ph[p], 16);
         }
-    if (d->len != need) return fail(ctx, NORM_E_INVALID_ARG, "inflated length does not match the image geometry");
+    for (uint32_t i = 0; i < n; ++i) {
+        const NormInflatedDesc &e = descs[i];
+        if (!e.data) return fail(ctx, NORM_E_INVALID_ARG, "inflated data is NULL");
+        if (e.width != w || e.height != h || e.bit_depth != d->bit_depth || e.color_type != d->color_type ||
+            e.interlace != d->interlace)
+            return fail(ctx, NORM_E_INVALID_ARG, "images of a batch must share width, height, bit depth, colour type and interlace");
+        if (e.len != need) return fail(ctx, NORM_E_INVALID_ARG, "inflated length does not match the image geometry");
+    }
     const size_t out_bytes = rowb(w) * h;
-    NORM_TRY(ensure_buf(ctx, ctx->inflated, align_up(need, 256)));
-    NORM_TRY(ensure_buf(ctx, ctx->passes, align_up(pass_bytes, 256) + align_up(ft_bytes, 256)));
-    if (d->interlace) NORM_TRY(ensure_buf(ctx, ctx->raw, align_up(out_bytes, 256)));
+    const size_t src_stride = align_up(need, 256), dst_stride = align_up(pass_bytes, 256), ft_stride = align_up(ft_bytes, 256),
+                 raw_stride = align_up(out_bytes, 256);
+    NORM_TRY(ensure_buf(ctx, ctx->inflated, src_stride * n));
+    NORM_TRY(ensure_buf(ctx, ctx->passes, (dst_stride + ft_stride) * n));
+    if (d->interlace) NORM_TRY(ensure_buf(ctx, ctx->raw, raw_stride * n));
     if (!ctx->d_status) CU_TRY(ctx, cudaMalloc(&ctx->d_status, sizeof(int32_t)));
     cudaStream_t s = ctx->main.stream;
     CU_TRY(ctx, cudaMemsetAsync(ctx->d_status, 0, sizeof(int32_t), s));
-    CU_TRY(ctx, cudaMemcpyAsync(ctx->inflated.p, d->data, need, cudaMemcpyHostToDevice, s));
+    for (uint32_t i = 0; i < n; ++i)
+        CU_TRY(ctx, cudaMemcpyAsync(static_cast<uint8_t *>(ctx->inflated.p) + i * src_stride, descs[i].data, need,
+                                    cudaMemcpyHostToDevice, s));
 
     UnfilterParams up;
     std::memset(&up, 0, sizeof(up));
     up.status = ctx->d_status;
+    up.nimg = n, up.src_stride = src_stride, up.dst_stride = dst_stride, up.ft_stride = ft_stride;
     DeinterlaceParams dp;
     std::memset(&dp, 0, sizeof(dp));
-    size_t soff = 0, poff = 0, foff = align_up(pass_bytes, 256);
+    uint8_t *ft_base = static_cast<uint8_t *>(ctx->passes.p) + dst_stride * n;
+    size_t soff = 0, poff = 0, foff = 0;
     uint32_t max_items = 1;
     for (int p = 0; p < npass; ++p) {
         if (!pw[p] || !ph[p]) continue;
         UnfilterPass &ps = up.pass[up.npass++];
         ps.src = static_cast<const uint8_t *>(ctx->inflated.p) + soff;
         ps.dst = static_cast<uint8_t *>(ctx->passes.p) + poff;
-        ps.ftype = static_cast<uint8_t *>(ctx->passes.p) + foff;
+        ps.ftype = ft_base + foff;
         ps.rows = ph[p], ps.row_bytes = (uint32_t)rowb(pw[p]), ps.pitch = (uint32_t)align_up(rowb(pw[p]), 16), ps.bpp = bpp;
         dp.pass_px[p] = ps.dst, dp.pass_row_bytes[p] = ps.pitch;
         soff += (size_t)ph[p] * (1 + rowb(pw[p]));
@@ -1017,27 +1033,44 @@ static norm_status unfilter_to_device(norm_ctx *ctx, const NormInflatedDesc *d, 
         foff += align_up(ph[p], 16);
         max_items = std::max<uint32_t>(max_items, (uint32_t)(((size_t)ps.pitch / 4 * ps.rows + 255) / 256));
     }
-    unfilter_align_kernel<<<dim3(std::min<uint32_t>(max_items, (uint32_t)ctx->sm_count * 8), up.npass), 256, 0, s>>>(up);
-    LAUNCH_CHECK(ctx);
-    switch (bpp) {
-    case 1: unfilter_wave_kernel<1><<<up.npass, kUnfThreads, 0, s>>>(up); break;
-    case 2: unfilter_wave_kernel<2><<<up.npass, kUnfThreads, 0, s>>>(up); break;
-    case 3: unfilter_wave_kernel<3><<<up.npass, kUnfThreads, 0, s>>>(up); break;
-    case 4: unfilter_wave_kernel<4><<<up.npass, kUnfThreads, 0, s>>>(up); break;
-    case 6: unfilter_wave_kernel<6><<<up.npass, kUnfThreads, 0, s>>>(up); break;
-    default: unfilter_wave_kernel<8><<<up.npass, kUnfThreads, 0, s>>>(up); break;
-    }
-    LAUNCH_CHECK(ctx);
-    if (d->interlace) {
-        for (int p = 0; p < 7; ++p)
-            if (!dp.pass_px[p]) dp.pass_px[p] = static_cast<const uint8_t *>(ctx->passes.p);  // empty pass: never read
-        dp.dst = static_cast<uint8_t *>(ctx->raw.p);
-        dp.w = w, dp.h = h, dp.row_bytes = (uint32_t)rowb(w), dp.bits = bits;
-        deinterlace_kernel<<<grid_for(ctx, (out_bytes + 255) / 256, 8), 256, 0, s>>>(dp);
+    // grid.y / grid.z are limited to 65535; larger batches go in slices
+    for (uint32_t i0 = 0; i0 < n; i0 += 32768) {
+        const uint32_t cnt = std::min<uint32_t>(32768, n - i0);
+        UnfilterParams sl = up;
+        sl.nimg = cnt;
+        for (int p = 0; p < sl.npass; ++p)
+            sl.pass[p].src += i0 * src_stride, sl.pass[p].dst += i0 * dst_stride, sl.pass[p].ftype += i0 * ft_stride;
+        const uint32_t gx = std::max(1u, std::min<uint32_t>(max_items, (uint32_t)ctx->sm_count * 8 / std::min<uint32_t>(cnt, 64u)));
+        unfilter_align_kernel<<<dim3(gx, sl.npass, cnt), 256, 0, s>>>(sl);
         LAUNCH_CHECK(ctx);
-        *dev_out = static_cast<const uint8_t *>(ctx->raw.p), *pitch_out = rowb(w);
+        const dim3 wg(sl.npass, cnt);
+        switch (bpp) {
+        case 1: unfilter_wave_kernel<1><<<wg, kUnfThreads, 0, s>>>(sl); break;
+        case 2: unfilter_wave_kernel<2><<<wg, kUnfThreads, 0, s>>>(sl); break;
+        case 3: unfilter_wave_kernel<3><<<wg, kUnfThreads, 0, s>>>(sl); break;
+        case 4: unfilter_wave_kernel<4><<<wg, kUnfThreads, 0, s>>>(sl); break;
+        case 6: unfilter_wave_kernel<6><<<wg, kUnfThreads, 0, s>>>(sl); break;
+        default: unfilter_wave_kernel<8><<<wg, kUnfThreads, 0, s>>>(sl); break;
+        }
+        LAUNCH_CHECK(ctx);
+        if (d->interlace) {
+            DeinterlaceParams dq = dp;
+            for (int p = 0; p < 7; ++p) {
+                if (!dq.pass_px[p]) dq.pass_px[p] = static_cast<const uint8_t *>(ctx->passes.p);  // empty pass: never read
+                else dq.pass_px[p] += i0 * dst_stride;
+            }
+            dq.dst = static_cast<uint8_t *>(ctx->raw.p) + i0 * raw_stride;
+            dq.w = w, dq.h = h, dq.row_bytes = (uint32_t)rowb(w), dq.bits = bits;
+            dq.pass_stride = dst_stride, dq.dst_stride = raw_stride;
+            const unsigned gdx = std::max(1u, grid_for(ctx, (out_bytes + 255) / 256, 8) / std::min<uint32_t>(cnt, 64u));
+            deinterlace_kernel<<<dim3(gdx, cnt), 256, 0, s>>>(dq);
+            LAUNCH_CHECK(ctx);
+        }
+    }
+    if (d->interlace) {
+        *dev_out = static_cast<const uint8_t *>(ctx->raw.p), *pitch_out = rowb(w), *img_stride_out = raw_stride;
     } else {
-        *dev_out = up.pass[0].dst, *pitch_out = up.pass[0].pitch;
+        *dev_out = up.pass[0].dst, *pitch_out = up.pass[0].pitch, *img_stride_out = dst_stride;
     }
     int32_t st = 0;
     CU_TRY(ctx, cudaMemcpyAsync(&st, ctx->d_status, sizeof(st), cudaMemcpyDeviceToHost, s));
@@ -1050,29 +1083,39 @@ static norm_status unfilter_to_device(norm_ctx *ctx, const NormInflatedDesc *d, 
 norm_status norm_cuda_unfilter(norm_ctx *ctx, const NormInflatedDesc *d, uint8_t *pixel_buffer) {
     NORM_TRY(bind(ctx));
     if (!pixel_buffer) return fail(ctx, NORM_E_INVALID_ARG, "pixel_buffer is NULL");
-    size_t rb = 0, pitch = 0;
+    size_t rb = 0, pitch = 0, stride = 0;
     const uint8_t *dev = nullptr;
-    NORM_TRY(unfilter_to_device(ctx, d, &dev, &pitch, &rb));
+    NORM_TRY(unfilter_to_device(ctx, d, 1, &dev, &pitch, &rb, &stride));
     CU_TRY(ctx, cudaMemcpy2DAsync(pixel_buffer, rb, dev, pitch, rb, d->height, cudaMemcpyDeviceToHost, ctx->main.stream));
+    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
+    return NORM_OK;
+}
+
+norm_status norm_cuda_unfilter_expand_rgba8_batch(norm_ctx *ctx, const NormInflatedDesc *descs, uint32_t n, const uint8_t *plte,
+                                                  int32_t n_plte, const uint8_t *trns, int32_t n_trns, int32_t mode,
+                                                  norm_img *out, uint32_t frame0) {
+    NORM_TRY(bind(ctx));
+    if (!out) return fail(ctx, NORM_E_INVALID_ARG, "out is NULL");
+    if (n == 0 || (uint64_t)frame0 + n > out->v.frames) return fail(ctx, NORM_E_INVALID_ARG, "frame range outside the image");
+    size_t rb = 0, pitch = 0, stride = 0;
+    const uint8_t *dev = nullptr;
+    NORM_TRY(unfilter_to_device(ctx, descs, n, &dev, &pitch, &rb, &stride));
+    NormPngDesc png;
+    std::memset(&png, 0, sizeof(png));
+    png.width = descs->width, png.height = descs->height, png.bit_depth = descs->bit_depth, png.color_type = descs->color_type;
+    png.len = pitch * descs->height;
+    png.plte = plte, png.n_plte = n_plte, png.trns = trns, png.n_trns = n_trns;
+    for (uint32_t i = 0; i < n; ++i) {
+        png.pixels = dev + (size_t)i * stride;
+        NORM_TRY(expand_impl(ctx, &png, mode, out->v, frame0 + i, /*pixels_on_device=*/true, pitch));
+    }
     CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
     return NORM_OK;
 }
 
 norm_status norm_cuda_unfilter_expand_rgba8(norm_ctx *ctx, const NormInflatedDesc *d, const uint8_t *plte, int32_t n_plte,
                                             const uint8_t *trns, int32_t n_trns, int32_t mode, norm_img *out, uint32_t frame) {
-    NORM_TRY(bind(ctx));
-    if (!out) return fail(ctx, NORM_E_INVALID_ARG, "out is NULL");
-    size_t rb = 0, pitch = 0;
-    const uint8_t *dev = nullptr;
-    NORM_TRY(unfilter_to_device(ctx, d, &dev, &pitch, &rb));
-    NormPngDesc png;
-    std::memset(&png, 0, sizeof(png));
-    png.width = d->width, png.height = d->height, png.bit_depth = d->bit_depth, png.color_type = d->color_type;
-    png.pixels = dev, png.len = pitch * d->height;
-    png.plte = plte, png.n_plte = n_plte, png.trns = trns, png.n_trns = n_trns;
-    NORM_TRY(expand_impl(ctx, &png, mode, out->v, frame, /*pixels_on_device=*/true, pitch));
-    CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
-    return NORM_OK;
+    return norm_cuda_unfilter_expand_rgba8_batch(ctx, d, d ? 1u : 0u, plte, n_plte, trns, n_trns, mode, out, frame);
 }
 
 // ---- encoder-side scanline filtering ---------------------------------------

@@ -25,15 +25,27 @@ struct UnfilterPass {
     uint32_t rows, row_bytes, pitch, bpp;
 };
 
+// A batch holds `nimg` images of identical geometry: pass[] describes image 0 and image i sits
+// src_stride / dst_stride / ft_stride bytes further in the three buffers.
 struct UnfilterParams {
     UnfilterPass pass[7];
     int32_t npass;
+    uint32_t nimg;
+    size_t src_stride, dst_stride, ft_stride;
     int32_t *status;  // set to 1 if a filter-type byte is > 4
 };
 
+__device__ __forceinline__ UnfilterPass pass_of(const UnfilterParams &p, uint32_t pass, uint32_t img) {
+    UnfilterPass ps = p.pass[pass];
+    ps.src += (size_t)img * p.src_stride;
+    ps.dst += (size_t)img * p.dst_stride;
+    ps.ftype += (size_t)img * p.ft_stride;
+    return ps;
+}
+
 // Step 1 (fully parallel): strip the filter-type bytes and re-align every row to a 16-byte pitch.
 __global__ void __launch_bounds__(256) unfilter_align_kernel(const __grid_constant__ UnfilterParams p) {
-    const UnfilterPass ps = p.pass[blockIdx.y];
+    const UnfilterPass ps = pass_of(p, blockIdx.y, blockIdx.z);
     const uint32_t words = ps.pitch / 4;
     const size_t total = (size_t)words * ps.rows;
     for (size_t it = (size_t)blockIdx.x * blockDim.x + threadIdx.x; it < total; it += (size_t)gridDim.x * blockDim.x) {
@@ -74,7 +86,7 @@ __device__ __forceinline__ uint32_t byte_of(const uint4 &v, int i) {
 template <int BPP>
 __global__ void __launch_bounds__(kUnfThreads) unfilter_wave_kernel(const __grid_constant__ UnfilterParams p) {
     __shared__ uint4 slot[2][kUnfThreads];
-    const UnfilterPass ps = p.pass[blockIdx.x];
+    const UnfilterPass ps = pass_of(p, blockIdx.x, blockIdx.y);
     if (ps.rows == 0 || ps.row_bytes == 0) return;
     const int t = threadIdx.x;
     const uint32_t nchunks = ps.pitch / 16;
@@ -149,6 +161,7 @@ struct DeinterlaceParams {
     uint32_t pass_row_bytes[7];
     uint8_t *dst;               // raster rows
     uint32_t w, h, row_bytes, bits;  // bits per pixel
+    size_t pass_stride, dst_stride;  // image blockIdx.y of a batch sits this far into the two buffers
 };
 
 // the Adam7 pass whose lattice contains pixel (x, y); the seven lattices partition the image
@@ -168,13 +181,15 @@ __device__ __forceinline__ int adam7_pass_of(uint32_t x, uint32_t y, uint32_t &p
 
 __global__ void __launch_bounds__(256) deinterlace_kernel(const __grid_constant__ DeinterlaceParams p) {
     const size_t total = (size_t)p.row_bytes * p.h;
+    const size_t poff = (size_t)blockIdx.y * p.pass_stride;
+    uint8_t *dst = p.dst + (size_t)blockIdx.y * p.dst_stride;
     for (size_t it = (size_t)blockIdx.x * blockDim.x + threadIdx.x; it < total; it += (size_t)gridDim.x * blockDim.x) {
         const uint32_t y = (uint32_t)(it / p.row_bytes), bx = (uint32_t)(it - (size_t)y * p.row_bytes);
         uint32_t outb = 0, px, py;
         if (p.bits >= 8) {
             const uint32_t bytes = p.bits / 8, x = bx / bytes, off = bx - x * bytes;
             const int ps = adam7_pass_of(x, y, px, py);
-            outb = p.pass_px[ps][(size_t)py * p.pass_row_bytes[ps] + (size_t)px * bytes + off];
+            outb = p.pass_px[ps][poff + (size_t)py * p.pass_row_bytes[ps] + (size_t)px * bytes + off];
         } else {
             const uint32_t per = 8 / p.bits, mask = (1u << p.bits) - 1u;
             for (uint32_t i = 0; i < per; ++i) {
@@ -182,11 +197,11 @@ __global__ void __launch_bounds__(256) deinterlace_kernel(const __grid_constant_
                 if (x >= p.w) break;
                 const int ps = adam7_pass_of(x, y, px, py);
                 const uint32_t bit = px * p.bits;
-                const uint32_t v = (p.pass_px[ps][(size_t)py * p.pass_row_bytes[ps] + (bit >> 3)] >> (8 - p.bits - (bit & 7))) & mask;
+                const uint32_t v = (p.pass_px[ps][poff + (size_t)py * p.pass_row_bytes[ps] + (bit >> 3)] >> (8 - p.bits - (bit & 7))) & mask;
                 outb |= v << (8 - p.bits - i * p.bits);
             }
         }
-        p.dst[it] = (uint8_t)outb;
+        dst[it] = (uint8_t)outb;
     }
 }
 

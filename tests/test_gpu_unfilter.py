@@ -122,3 +122,67 @@ def test_unfilter_errors(ctx):
         ctx.unfilter(4, 2, 8, 0, 0, raw[:-1])
     with pytest.raises(nb.NormError):  # bad depth for RGB
         ctx.unfilter(4, 2, 4, 2, 0, raw)
+
+
+# ---- batches: n streams of identical geometry, one CTA per (image, pass) ---------------------
+
+def _groups():
+    g = {}
+    for name in VALID:
+        w, h, bd, ct, il, raw, plte, trns = inflate_png(os.path.join(PNGSUITE, name + ".png"))
+        if ct != 3 and len(trns) == 0:  # palette / colour key are per file; a batch shares them
+            g.setdefault((w, h, bd, ct, il), []).append(name)
+    return {k: v for k, v in g.items() if len(v) >= 2}
+
+
+GROUPS = _groups()
+
+
+@pytest.mark.parametrize("key", sorted(GROUPS), ids=lambda k: "%dx%d_bd%d_ct%d_il%d" % k)
+def test_unfilter_batch_pngsuite(ctx, oracle, key):
+    w, h, bd, ct, il = key
+    names = GROUPS[key]
+    streams = [inflate_png(os.path.join(PNGSUITE, n + ".png"))[5] for n in names]
+    out = ctx.image_create(w, h, len(names) + 1)
+    ctx.unfilter_expand_batch(w, h, bd, ct, il, streams, nb.NORM_EXPAND_SPEC, out, 1)
+    got = out.download()
+    for i, n in enumerate(names):
+        d = oracle.png_decode(open(os.path.join(PNGSUITE, n + ".png"), "rb").read())
+        assert np.array_equal(got[1 + i], oracle.expand_rgba8(d, oracle.EXPAND_SPEC)), n
+    out.destroy()
+
+
+def test_unfilter_batch_round_trip_through_gpu_filter(ctx):
+    """frames -> GPU filter selection (all five types appear) -> batched GPU unfilter + expansion."""
+    from conftest import smooth_rgba
+    rng = np.random.default_rng(5)
+    w, h, n = 257, 600, 9
+    frames = [(smooth_rgba(w, h, seed=s)[..., :3] + rng.integers(0, 3, size=(h, w, 3))).astype(np.uint8) for s in range(n)]
+    streams, used = [], set()
+    for f in frames:
+        st, ft = ctx.filter_scanlines(w, h, 8, 2, f)
+        streams.append(st.tobytes())
+        used |= set(ft.tolist())
+    assert len(used) >= 3
+    out = ctx.image_create(w, h, n)
+    ctx.unfilter_expand_batch(w, h, 8, 2, 0, streams, nb.NORM_EXPAND_COMPAT, out)
+    got = out.download()
+    for i, f in enumerate(frames):
+        assert np.array_equal(got[i][..., :3], f) and (got[i][..., 3] == 0).all()
+    out.destroy()
+
+
+def test_unfilter_batch_errors(ctx):
+    good = bytes([0]) + bytes(4) + bytes([2]) + bytes(4)
+    bad = bytes([0]) + bytes(4) + bytes([7]) + bytes(4)
+    out = ctx.image_create(4, 2, 3)
+    with pytest.raises(nb.NormError) as e:  # invalid filter byte in the last image of the batch
+        ctx.unfilter_expand_batch(4, 2, 8, 0, 0, [good, good, bad], nb.NORM_EXPAND_SPEC, out)
+    assert "filter" in str(e.value)
+    with pytest.raises(nb.NormError):  # more streams than frames
+        ctx.unfilter_expand_batch(4, 2, 8, 0, 0, [good] * 4, nb.NORM_EXPAND_SPEC, out)
+    with pytest.raises(nb.NormError):  # one stream of the wrong length
+        ctx.unfilter_expand_batch(4, 2, 8, 0, 0, [good, good[:-1]], nb.NORM_EXPAND_SPEC, out)
+    ctx.unfilter_expand_batch(4, 2, 8, 0, 0, [good, good, good], nb.NORM_EXPAND_SPEC, out)
+    assert (out.download()[..., :3] == 0).all()
+    out.destroy()
