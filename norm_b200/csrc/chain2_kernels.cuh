@@ -212,22 +212,37 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
             C2_ITEM_GEOMETRY();
             const uint8_t *in_frame = p.in.ptr + (size_t)f * p.in.frame_stride;
-            const int st_x = x0 - C::HL + 4 * st_c4;
-            const bool st_vec = st_x >= 0 && st_x + 3 <= W - 1;
-            const int xc0 = clampi(st_x, 0, W - 1), xc1 = clampi(st_x + 1, 0, W - 1), xc2 = clampi(st_x + 2, 0, W - 1),
-                      xc3 = clampi(st_x + 3, 0, W - 1);
+            const uint32_t pitch32 = (uint32_t)p.in.pitch;
 
-            // cp.async one batch of source rows (ClampToEdge in x and y) into staging buffer `buf`
+            // cp.async one batch of source rows (ClampToEdge in x and y) into staging buffer `buf`.
+            // Everything but the frame base is recomputed here so that nothing stays live (or gets
+            // spilled) across the H pass; the row loop is unrolled and costs a clamp, one 32x32+64
+            // multiply-add and the copy per 16-byte chunk.
             auto stage_issue = [&](int bb, int buf) {
                 if (st_rg < NRG) {
-                    const uint32_t d0 = (uint32_t)__cvta_generic_to_shared(stg_base + buf * (C::RB * C::STG_STRIDE) + 4 * st_c4);
-                    for (int j = st_rg; j < C::RB; j += NRG) {
-                        const int sy = clampi(o_lo - C::M + bb * C::RB + j, 0, Himg - 1);
-                        const uint32_t *row = reinterpret_cast<const uint32_t *>(in_frame + (size_t)sy * p.in.pitch);
-                        const uint32_t d = d0 + j * (C::STG_STRIDE * 4);
-                        if (st_vec) {
-                            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(row + st_x) : "memory");
-                        } else {
+                    constexpr int KMAX = (C::RB + NRG - 1) / NRG;
+                    const int st_x = x0 - C::HL + 4 * st_c4;
+                    const uint32_t d0 = (uint32_t)__cvta_generic_to_shared(stg_base + buf * (C::RB * C::STG_STRIDE) + 4 * st_c4) +
+                                        (uint32_t)st_rg * (C::STG_STRIDE * 4);
+                    const int r0 = o_lo - C::M + bb * C::RB + st_rg;
+                    if (st_x >= 0 && st_x + 3 <= W - 1) {
+                        const uint8_t *src0 = in_frame + (size_t)st_x * 4;
+#pragma unroll
+                        for (int k = 0; k < KMAX; ++k) {
+                            if (st_rg + k * NRG < C::RB) {
+                                const uint32_t sy = (uint32_t)clampi(r0 + k * NRG, 0, Himg - 1);
+                                const uint8_t *src = src0 + (uint64_t)sy * pitch32;
+                                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d0 + k * NRG * (C::STG_STRIDE * 4)), "l"(src)
+                                             : "memory");
+                            }
+                        }
+                    } else {
+                        const int xc0 = clampi(st_x, 0, W - 1), xc1 = clampi(st_x + 1, 0, W - 1), xc2 = clampi(st_x + 2, 0, W - 1),
+                                  xc3 = clampi(st_x + 3, 0, W - 1);
+                        for (int k = 0; st_rg + k * NRG < C::RB; ++k) {
+                            const uint32_t sy = (uint32_t)clampi(r0 + k * NRG, 0, Himg - 1);
+                            const uint32_t *row = reinterpret_cast<const uint32_t *>(in_frame + (uint64_t)sy * pitch32);
+                            const uint32_t d = d0 + k * NRG * (C::STG_STRIDE * 4);
                             asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(row + xc0) : "memory");
                             asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 4), "l"(row + xc1) : "memory");
                             asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 8), "l"(row + xc2) : "memory");
@@ -403,6 +418,8 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(NORM_C2_REGS_C));
         const int tc = tid - 2 * kC2Group;  // output column of the strip
         const int lane = tc & 31, warp = tc >> 5;
+        // shared-memory address of lumaLut minus 4 * (bits of 1.5*2^23), modulo 2^32: lut_biased + 4*bits = &lumaLut[byte]
+        const uint32_t lut_biased = (uint32_t)__cvta_generic_to_shared(lumaLut) - (kMagicBits << 2);
 
         bar_arrive(kB2IEmpty0, 2 * kC2Group);  // both intensity slots start out empty
         bar_arrive(kB2IEmpty1, 2 * kC2Group);
@@ -414,26 +431,33 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
             const int xl = min(x, W - 1);  // keeps addresses valid on idle lanes
             // intensity column of x is tc+1; ClampToEdge: column -1 reads column 0, column W reads column W-1
             const int il = (x - 1 < 0) ? tc + 1 : tc, ic = min(tc + 1, C::IS - 1), ir = (x + 1 > W - 1) ? ic : min(tc + 2, C::IS - 1);
-            const uint8_t *ip = p.in.ptr + (size_t)f * p.in.frame_stride + (size_t)ya * p.in.pitch + (size_t)xl * 4;
+            const uint8_t *ipf = p.in.ptr + (size_t)f * p.in.frame_stride + (size_t)xl * 4;  // column xl of the frame
+            const uint32_t ipitch = (uint32_t)p.in.pitch;
+            // source pixel of row r for the SSIM (L2-resident: group A staged that row a few batches ago)
+            auto src_px = [&](int r) {
+                return *reinterpret_cast<const uint32_t *>(ipf + (uint64_t)(uint32_t)min(r, Himg - 1) * ipitch);
+            };
             uint32_t *op = reinterpret_cast<uint32_t *>(p.out.ptr + (size_t)f * p.out.frame_stride + (size_t)ya * p.out.pitch) + xl;
             const bool ssim_on = p.do_ssim && writes;
-            uint32_t spx_next = *reinterpret_cast<const uint32_t *>(ip);  // source pixel of row ya (L2-resident)
+            uint32_t sp0 = src_px(ya), sp1 = src_px(ya + 1), sp2 = src_px(ya + 2);  // three rows in flight
             double m5[5] = {0, 0, 0, 0, 0};
             // 3x3 window rows as (left, centre, right) triples; w0 = row o-2, w1 = row o-1 between steps
             float w0l = 0, w0c = 0, w0r = 0, w1l = 0, w1c = 0, w1r = 0, w2l, w2c, w2r;
             int y = ya;  // next output row
 
-// one output row: Sobel(top, mid, bottom), store, SSIM; PREFETCH fetches the next row's source pixel
-#define C2_EMIT(TL, TC, TR, ML, MR, BL, BC, BR, PREFETCH)                                                   \
+// one output row: Sobel(top, mid, bottom), store, SSIM against source pixel SPX.
+// The quantised magnitude stays inside the bits of (c + 1.5*2^23): one PRMT builds the (c,c,c,255) pixel
+// and the luma table is addressed as lut_biased + 4*bits (the constant prefix is folded into the base).
+#define C2_EMIT(TL, TC, TR, ML, MR, BL, BC, BR, SPX, SSCOND)                                                \
     {                                                                                                       \
-        const uint32_t spx = spx_next;                                                                      \
-        ip += p.in.pitch;                                                                                   \
-        if (PREFETCH) spx_next = *reinterpret_cast<const uint32_t *>(ip);                                   \
-        const uint32_t cq = sobel_mag_fast(TL, TC, TR, ML, MR, BL, BC, BR);                                 \
-        if (writes) *op = cq * 0x010101u | 0xff000000u;                                                     \
+        const uint32_t spx = SPX;                                                                           \
+        const uint32_t cb = sobel_mag_bits(TL, TC, TR, ML, MR, BL, BC, BR);                                 \
+        if (writes) *op = __byte_perm(cb, 0xffu, 0x4000);                                                   \
         op = reinterpret_cast<uint32_t *>(reinterpret_cast<uint8_t *>(op) + p.out.pitch);                   \
-        if (ssim_on && (uint32_t)(y - (int)p.ssim_y0) < p.ssim_y1 - p.ssim_y0) {                            \
-            const double xv = (double)lumaLut[cq], yv = (double)luma_ssim(spx);                             \
+        if (SSCOND) {                                                                                       \
+            float lx;                                                                                       \
+            asm("ld.shared.f32 %0, [%1];" : "=f"(lx) : "r"(lut_biased + (cb << 2)));                        \
+            const double xv = (double)lx, yv = (double)luma_ssim(spx);                                      \
             m5[0] += xv;                                                                                    \
             m5[1] += yv;                                                                                    \
             m5[2] = fma(xv, xv, m5[2]);                                                                     \
@@ -442,6 +466,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         }                                                                                                   \
         ++y;                                                                                                \
     }
+#define C2_ROWTEST (ssim_on && (uint32_t)(y - (int)p.ssim_y0) < p.ssim_y1 - p.ssim_y0)
 
             for (int b = 0; b < nbatch; ++b, ++g) {
                 const int slot = (int)(g & 1u);
@@ -460,21 +485,41 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                     w0l = w1l, w0c = w1c, w0r = w1r;
                     w1l = w2l, w1c = w2c, w1r = w2r;
                 }
-                // main: three rows per trip, window registers rotate statically
-                for (; j + 3 <= j_hi; j += 3) {
-                    const float *rp = ist + j * C::IS;
-                    w2l = rp[il], w2c = rp[ic], w2r = rp[ir];
-                    C2_EMIT(w2l, w2c, w2r, w1l, w1r, w0l, w0c, w0r, true);
-                    w0l = rp[C::IS + il], w0c = rp[C::IS + ic], w0r = rp[C::IS + ir];
-                    C2_EMIT(w0l, w0c, w0r, w2l, w2r, w1l, w1c, w1r, true);
-                    w1l = rp[2 * C::IS + il], w1c = rp[2 * C::IS + ic], w1r = rp[2 * C::IS + ir];
-                    C2_EMIT(w1l, w1c, w1r, w0l, w0r, w2l, w2c, w2r, true);
+                // main: three rows per trip, window registers rotate statically.  When every row this batch
+                // emits lies inside the SSIM row range (always, outside band mode) the per-row test is dropped.
+                if (y >= (int)p.ssim_y0 && y + (j_hi - j) <= (int)p.ssim_y1) {
+                    for (; j + 3 <= j_hi; j += 3) {
+                        const float *rp = ist + j * C::IS;
+                        w2l = rp[il], w2c = rp[ic], w2r = rp[ir];
+                        C2_EMIT(w2l, w2c, w2r, w1l, w1r, w0l, w0c, w0r, sp0, ssim_on);
+                        sp0 = src_px(y + 2);  // y already counts the row just emitted: this is row (emitted + 3)
+                        w0l = rp[C::IS + il], w0c = rp[C::IS + ic], w0r = rp[C::IS + ir];
+                        C2_EMIT(w0l, w0c, w0r, w2l, w2r, w1l, w1c, w1r, sp1, ssim_on);
+                        sp1 = src_px(y + 2);
+                        w1l = rp[2 * C::IS + il], w1c = rp[2 * C::IS + ic], w1r = rp[2 * C::IS + ir];
+                        C2_EMIT(w1l, w1c, w1r, w0l, w0r, w2l, w2c, w2r, sp2, ssim_on);
+                        sp2 = src_px(y + 2);
+                    }
+                } else {
+                    for (; j + 3 <= j_hi; j += 3) {
+                        const float *rp = ist + j * C::IS;
+                        w2l = rp[il], w2c = rp[ic], w2r = rp[ir];
+                        C2_EMIT(w2l, w2c, w2r, w1l, w1r, w0l, w0c, w0r, sp0, C2_ROWTEST);
+                        sp0 = src_px(y + 2);  // y already counts the row just emitted: this is row (emitted + 3)
+                        w0l = rp[C::IS + il], w0c = rp[C::IS + ic], w0r = rp[C::IS + ir];
+                        C2_EMIT(w0l, w0c, w0r, w2l, w2r, w1l, w1c, w1r, sp1, C2_ROWTEST);
+                        sp1 = src_px(y + 2);
+                        w1l = rp[2 * C::IS + il], w1c = rp[2 * C::IS + ic], w1r = rp[2 * C::IS + ir];
+                        C2_EMIT(w1l, w1c, w1r, w0l, w0r, w2l, w2c, w2r, sp2, C2_ROWTEST);
+                        sp2 = src_px(y + 2);
+                    }
                 }
                 // remainder rows
                 for (; j < j_hi; ++j) {
                     const float *rp = ist + j * C::IS;
                     w2l = rp[il], w2c = rp[ic], w2r = rp[ir];
-                    C2_EMIT(w2l, w2c, w2r, w1l, w1r, w0l, w0c, w0r, true);
+                    C2_EMIT(w2l, w2c, w2r, w1l, w1r, w0l, w0c, w0r, sp0, C2_ROWTEST);
+                    sp0 = sp1, sp1 = sp2, sp2 = src_px(y + 2);
                     w0l = w1l, w0c = w1c, w0r = w1r;
                     w1l = w2l, w1c = w2c, w1r = w2r;
                 }
@@ -482,8 +527,9 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                 bar_arrive(kB2IEmpty0 + slot, 2 * kC2Group);
             }
             // bottom edge of the image: row H-1 reads row H (clamped) = row H-1
-            if (yb == Himg) C2_EMIT(w1l, w1c, w1r, w1l, w1r, w0l, w0c, w0r, false);
+            if (yb == Himg) C2_EMIT(w1l, w1c, w1r, w1l, w1r, w0l, w0c, w0r, sp0, C2_ROWTEST);
 #undef C2_EMIT
+#undef C2_ROWTEST
             if (p.do_ssim) {
 #pragma unroll
                 for (int k = 0; k < 5; ++k) {

@@ -17,7 +17,10 @@ ap.add_argument("--width", type=int, default=1920)
 ap.add_argument("--height", type=int, default=1080)
 ap.add_argument("--gray", type=int, default=0)
 ap.add_argument("--no-ssim", action="store_true")
+ap.add_argument("--lib", default=None, help="alternative libnorm_cuda.so (A/B runs)")
 a = ap.parse_args()
+if a.lib:
+    nb._lib.LIB_PATH = os.path.abspath(a.lib)
 W, H, n = a.width, a.height, a.frames
 src_t = torch.randint(0, 256, (n, H, W, 4), dtype=torch.uint8, device="cuda")
 dst_t = torch.empty_like(src_t)
