@@ -431,15 +431,22 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
             const int xl = min(x, W - 1);  // keeps addresses valid on idle lanes
             // intensity column of x is tc+1; ClampToEdge: column -1 reads column 0, column W reads column W-1
             const int il = (x - 1 < 0) ? tc + 1 : tc, ic = min(tc + 1, C::IS - 1), ir = (x + 1 > W - 1) ? ic : min(tc + 2, C::IS - 1);
-            const uint8_t *ipf = p.in.ptr + (size_t)f * p.in.frame_stride + (size_t)xl * 4;  // column xl of the frame
-            const uint32_t ipitch = (uint32_t)p.in.pitch;
-            // source pixel of row r for the SSIM (L2-resident: group A staged that row a few batches ago)
-            auto src_px = [&](int r) {
-                return *reinterpret_cast<const uint32_t *>(ipf + (uint64_t)(uint32_t)min(r, Himg - 1) * ipitch);
-            };
+            // source pixels for the SSIM, three rows in flight (L2-resident: group A staged those rows a few
+            // batches ago).  ipn walks down column xl one row per emitted row and stops at the last image row.
+            const uint8_t *ipn = p.in.ptr + (size_t)f * p.in.frame_stride + (size_t)ya * p.in.pitch + (size_t)xl * 4;
             uint32_t *op = reinterpret_cast<uint32_t *>(p.out.ptr + (size_t)f * p.out.frame_stride + (size_t)ya * p.out.pitch) + xl;
             const bool ssim_on = p.do_ssim && writes;
-            uint32_t sp0 = src_px(ya), sp1 = src_px(ya + 1), sp2 = src_px(ya + 2);  // three rows in flight
+            uint32_t sp0, sp1, sp2;
+            sp0 = *reinterpret_cast<const uint32_t *>(ipn);
+            if (ya + 1 < Himg) ipn += p.in.pitch;
+            sp1 = *reinterpret_cast<const uint32_t *>(ipn);
+            if (ya + 2 < Himg) ipn += p.in.pitch;
+            sp2 = *reinterpret_cast<const uint32_t *>(ipn);
+            if (ya + 3 < Himg) ipn += p.in.pitch;
+// next source pixel; y already counts the row just emitted, the pixel fetched belongs to row y + 2
+#define C2_NEXT_SRC(DST)                                   \
+    DST = *reinterpret_cast<const uint32_t *>(ipn);        \
+    if (y + 3 < Himg) ipn += p.in.pitch;
             double m5[5] = {0, 0, 0, 0, 0};
             // 3x3 window rows as (left, centre, right) triples; w0 = row o-2, w1 = row o-1 between steps
             float w0l = 0, w0c = 0, w0r = 0, w1l = 0, w1c = 0, w1r = 0, w2l, w2c, w2r;
@@ -492,26 +499,26 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                         const float *rp = ist + j * C::IS;
                         w2l = rp[il], w2c = rp[ic], w2r = rp[ir];
                         C2_EMIT(w2l, w2c, w2r, w1l, w1r, w0l, w0c, w0r, sp0, ssim_on);
-                        sp0 = src_px(y + 2);  // y already counts the row just emitted: this is row (emitted + 3)
+                        C2_NEXT_SRC(sp0)
                         w0l = rp[C::IS + il], w0c = rp[C::IS + ic], w0r = rp[C::IS + ir];
                         C2_EMIT(w0l, w0c, w0r, w2l, w2r, w1l, w1c, w1r, sp1, ssim_on);
-                        sp1 = src_px(y + 2);
+                        C2_NEXT_SRC(sp1)
                         w1l = rp[2 * C::IS + il], w1c = rp[2 * C::IS + ic], w1r = rp[2 * C::IS + ir];
                         C2_EMIT(w1l, w1c, w1r, w0l, w0r, w2l, w2c, w2r, sp2, ssim_on);
-                        sp2 = src_px(y + 2);
+                        C2_NEXT_SRC(sp2)
                     }
                 } else {
                     for (; j + 3 <= j_hi; j += 3) {
                         const float *rp = ist + j * C::IS;
                         w2l = rp[il], w2c = rp[ic], w2r = rp[ir];
                         C2_EMIT(w2l, w2c, w2r, w1l, w1r, w0l, w0c, w0r, sp0, C2_ROWTEST);
-                        sp0 = src_px(y + 2);  // y already counts the row just emitted: this is row (emitted + 3)
+                        C2_NEXT_SRC(sp0)
                         w0l = rp[C::IS + il], w0c = rp[C::IS + ic], w0r = rp[C::IS + ir];
                         C2_EMIT(w0l, w0c, w0r, w2l, w2r, w1l, w1c, w1r, sp1, C2_ROWTEST);
-                        sp1 = src_px(y + 2);
+                        C2_NEXT_SRC(sp1)
                         w1l = rp[2 * C::IS + il], w1c = rp[2 * C::IS + ic], w1r = rp[2 * C::IS + ir];
                         C2_EMIT(w1l, w1c, w1r, w0l, w0r, w2l, w2c, w2r, sp2, C2_ROWTEST);
-                        sp2 = src_px(y + 2);
+                        C2_NEXT_SRC(sp2)
                     }
                 }
                 // remainder rows
@@ -519,7 +526,8 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                     const float *rp = ist + j * C::IS;
                     w2l = rp[il], w2c = rp[ic], w2r = rp[ir];
                     C2_EMIT(w2l, w2c, w2r, w1l, w1r, w0l, w0c, w0r, sp0, C2_ROWTEST);
-                    sp0 = sp1, sp1 = sp2, sp2 = src_px(y + 2);
+                    sp0 = sp1, sp1 = sp2;
+                    C2_NEXT_SRC(sp2)
                     w0l = w1l, w0c = w1c, w0r = w1r;
                     w1l = w2l, w1c = w2c, w1r = w2r;
                 }
@@ -530,6 +538,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
             if (yb == Himg) C2_EMIT(w1l, w1c, w1r, w1l, w1r, w0l, w0c, w0r, sp0, C2_ROWTEST);
 #undef C2_EMIT
 #undef C2_ROWTEST
+#undef C2_NEXT_SRC
             if (p.do_ssim) {
 #pragma unroll
                 for (int k = 0; k < 5; ++k) {
