@@ -419,7 +419,8 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         const int tc = tid - 2 * kC2Group;  // output column of the strip
         const int lane = tc & 31, warp = tc >> 5;
         // shared-memory address of lumaLut minus 4 * (bits of 1.5*2^23), modulo 2^32: lut_biased + 4*bits = &lumaLut[byte]
-        const uint32_t lut_biased = (uint32_t)__cvta_generic_to_shared(lumaLut) - (kMagicBits << 2);
+        uint32_t lut_biased = (uint32_t)__cvta_generic_to_shared(lumaLut) - (kMagicBits << 2);
+        asm volatile("" : "+r"(lut_biased));  // keep it in a register: one LEA per lookup instead of LEA + add
 
         bar_arrive(kB2IEmpty0, 2 * kC2Group);  // both intensity slots start out empty
         bar_arrive(kB2IEmpty1, 2 * kC2Group);
