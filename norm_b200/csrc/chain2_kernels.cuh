@@ -37,9 +37,10 @@ constexpr int kC2Group = 128, kC2Threads = 3 * kC2Group;
 static_assert(NORM_C2_REGS_A + NORM_C2_REGS_B + NORM_C2_REGS_C == 240, "register budgets must sum to 3 x 80");
 
 // MODE 0: front -> blur -> Sobel (+ SSIM)   one blurred channel triple -> intensity -> group C
-// MODE 1: front -> blur                     group B writes the blurred RGBA8 itself, group C idles;
-//         all four channels are blurred (image_shader.wgsl:88-103 blurs alpha too); after
-//         grayscale the three colour channels coincide, so two distinct channels (y, a) remain
+// MODE 1: front -> blur                     all four channels are blurred (image_shader.wgsl:88-103 blurs
+//         alpha too); after grayscale the three colour channels coincide, so two distinct channels (y, a)
+//         remain.  The H pass is the larger half of the work here, so groups A and C both run it (half of
+//         the channels each, staging shared) and group B runs the V pass for all channels and stores RGBA8
 template <int R, bool GRAY, int MODE = 0>
 struct Fused2Cfg {
     static_assert(R % 2 == 1, "odd radii");
@@ -47,7 +48,7 @@ struct Fused2Cfg {
     static constexpr int HALO = MODE == 0 ? 1 : 0;      // Sobel needs one blurred pixel around each output
     static constexpr int SW = 120;                      // output columns per strip
     static constexpr int BW = SW + 2 * HALO;            // blurred / intensity columns
-    static constexpr int T = (MODE == 1 && !GRAY && R > 9) ? 8 : NORM_C2_T;  // H-pass outputs per thread (4-channel blur: fewer, for registers)
+    static constexpr int T = (MODE == 1 && !GRAY && R > 9) ? 8 : NORM_C2_T;  // H-pass outputs per thread (4-channel H pass: fewer, for registers)
     static constexpr int SEGS = (BW + T - 1) / T;       // 11
     static constexpr int HS = (BW + 3) / 4 * 4;         // 124: H plane row stride = columns actually stored
     static constexpr int HL = ((M + HALO) + 3) / 4 * 4; // staged left halo, 16-byte chunks
@@ -56,6 +57,17 @@ struct Fused2Cfg {
     static constexpr int STG_STRIDE = SRCW;             // words, multiple of 4
     static constexpr int RB = R * ((16 + R - 1) / R);   // rows per batch, multiple of R
     static constexpr int CH = MODE == 0 ? (GRAY ? 1 : 3) : (GRAY ? 2 : 4);
+    // MODE 1 after grayscale (channels y, alpha): groups A and C both run the H pass (one channel each, staging
+    // shared) and group B runs the V pass of both and stores RGBA8.  MODE 1 on RGBA: group A runs the H pass
+    // of all four channels and groups B and C the V pass of two channels each (2 x R running outputs), because
+    // 4 x R running outputs do not fit one thread's registers.
+    static constexpr int HGROUPS = (MODE == 1 && GRAY) ? 2 : 1;
+    static constexpr int VGROUPS = (MODE == 1 && !GRAY) ? 2 : 1;
+    static constexpr int CH_A = (MODE == 1 && GRAY) ? 1 : CH;   // channels of group A's H pass (from 0)
+    static constexpr int HTHREADS = HGROUPS * 128;
+    // register budgets (setmaxnreg), summing to 3 x 80
+    static constexpr int REGS_H = (MODE == 1 && !GRAY) ? 64 : NORM_C2_REGS_A;
+    static constexpr int REGS_V = (MODE == 1 && !GRAY) ? 88 : NORM_C2_REGS_B;
     // source byte of channel c: MODE 1 + GRAY blurs (y, alpha) = bytes (0, 3)
     __host__ __device__ static constexpr int chan_byte(int c) { return (MODE == 1 && GRAY && c == 1) ? 3 : c; }
     static constexpr int IS = 128;                      // intensity row stride
@@ -73,14 +85,63 @@ enum {
     kB2A = 9, kB2C = 10
 };
 
-// Blur-only consumer (MODE 1): V pass for channels [C0, C0+NCH) of one blurred column per thread and a
-// store of those bytes of the RGBA8 result.  On RGBA the four channels are split between groups B and C
-// (2 x R running outputs each); after grayscale group B takes both distinct channels (y, alpha).
-template <typename C, int R, bool GRAY, int C0, int NCH, int NCONS>
+// V pass of one batch for channels [C0, C0+NCH) of one blurred column (MODE 1): NCH x R running outputs in
+// registers (static rotation: the row loop is fully unrolled and RB % R == 0), quantise, store those bytes
+// of the RGBA8 result.  hp = H planes of this batch's slot at this thread's column.
+template <typename C, int R, bool GRAY, int C0, int NCH>
+__device__ __forceinline__ void v_pass_batch(const FusedParams &p, const float *hp, int b, int NB, bool in_image, uint8_t *orow,
+                                             float2 (*vacc2)[R / 2], float *vaccl) {
+#pragma unroll
+    for (int j = 0; j < C::RB; ++j) {
+        uint32_t q[NCH];
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            const float h = hp[((C0 + c) * C::RB + j) * C::HS];
+            const float2 h2 = make_float2(h, h);
+#pragma unroll
+            for (int i = 0; i < R / 2; ++i) {
+                const int k = ((j - 2 * i) % R + R) % R;  // tap of slot 2i; slot 2i+1 takes k-1 (mod R)
+                if (k >= 1)
+                    vacc2[c][i] = __ffma2_rn(p.tp[k], h2, vacc2[c][i]);
+                else
+                    vacc2[c][i] = __ffma2_rn(make_float2(p.taps.t[0], p.taps.t[R - 1]), h2, vacc2[c][i]);
+            }
+            vaccl[c] = __fmaf_rn(p.taps.t[(j + 1) % R], h, vaccl[c]);
+            const int done = (j + 1) % R;  // the output that just took its last tap
+            float o;
+            if (done == R - 1) {
+                o = vaccl[c], vaccl[c] = 0.0f;
+            } else if (done & 1) {
+                o = vacc2[c][done / 2].y, vacc2[c][done / 2].y = 0.0f;
+            } else {
+                o = vacc2[c][done / 2].x, vacc2[c][done / 2].x = 0.0f;
+            }
+            // blurred values lie in [0, 255.0001]: the 1.5*2^23 trick alone is round-half-even + clamp
+            q[c] = __float_as_uint(__fadd_rn(o, 12582912.0f)) & 0xffu;
+        }
+        const int n = b * C::RB + j - (R - 1);  // output row relative to the band's first row
+        if (n >= 0 && n < NB && in_image) {
+            uint8_t *px = orow + (size_t)n * p.out.pitch;
+            if constexpr (GRAY) {  // channels (y, alpha) -> (y, y, y, alpha)
+                *reinterpret_cast<uint32_t *>(px) = q[0] * 0x010101u | (q[NCH - 1] << 24);
+            } else if constexpr (NCH == 3) {  // r, g, b; the alpha byte comes from group C
+                *reinterpret_cast<uint16_t *>(px + C0) = (uint16_t)(q[0] | (q[1] << 8));
+                px[C0 + 2] = (uint8_t)q[2];
+            } else if constexpr (NCH == 1) {
+                px[C0] = (uint8_t)q[0];
+            } else {
+                *reinterpret_cast<uint16_t *>(px + C0) = (uint16_t)(q[0] | (q[NCH - 1] << 8));
+            }
+        }
+    }
+}
+
+// Blur-only consumer (MODE 1, group B): V pass for channels [C0, C0+NCH) of one blurred column per thread.
+// kParties = all threads that meet at the H-plane barriers (producing groups and this one).
+template <typename C, int R, bool GRAY, int C0, int NCH, int kParties>
 __device__ __forceinline__ void blur_only_consumer(const FusedParams &p, const float *Hb_base, int bcol, uint32_t items_per_frame,
                                                    size_t total) {
     constexpr int kHbFloats = C::CH * C::RB * C::HS;
-    constexpr int kParties = (1 + NCONS) * kC2Group;
     const int W = (int)p.in.w, Himg = (int)p.in.h;
     const bool active = bcol < C::BW;
     uint32_t g = 0;
@@ -107,47 +168,8 @@ __device__ __forceinline__ void blur_only_consumer(const FusedParams &p, const f
         for (int b = 0; b < nbatch; ++b, ++g) {
             const int slot = (int)(g & 1u);
             bar_sync(kB2Full0 + slot, kParties);
-            if (active) {
-                const float *hp = Hb_base + slot * kHbFloats + bcol;
-#pragma unroll
-                for (int j = 0; j < C::RB; ++j) {
-                    uint32_t q[NCH];
-#pragma unroll
-                    for (int c = 0; c < NCH; ++c) {
-                        const float h = hp[((C0 + c) * C::RB + j) * C::HS];
-                        const float2 h2 = make_float2(h, h);
-#pragma unroll
-                        for (int i = 0; i < R / 2; ++i) {
-                            const int k = ((j - 2 * i) % R + R) % R;
-                            if (k >= 1)
-                                vacc2[c][i] = __ffma2_rn(p.tp[k], h2, vacc2[c][i]);
-                            else
-                                vacc2[c][i] = __ffma2_rn(make_float2(p.taps.t[0], p.taps.t[R - 1]), h2, vacc2[c][i]);
-                        }
-                        vaccl[c] = __fmaf_rn(p.taps.t[(j + 1) % R], h, vaccl[c]);
-                        const int done = (j + 1) % R;
-                        float o;
-                        if (done == R - 1) {
-                            o = vaccl[c], vaccl[c] = 0.0f;
-                        } else if (done & 1) {
-                            o = vacc2[c][done / 2].y, vacc2[c][done / 2].y = 0.0f;
-                        } else {
-                            o = vacc2[c][done / 2].x, vacc2[c][done / 2].x = 0.0f;
-                        }
-                        // blurred values lie in [0, 255.0001]: the 1.5*2^23 trick alone is round-half-even + clamp
-                        q[c] = __float_as_uint(__fadd_rn(o, 12582912.0f)) & 0xffu;
-                    }
-                    const int n = b * C::RB + j - (R - 1);  // output row relative to ya
-                    if (n >= 0 && n < NB && bx < W) {
-                        uint8_t *px = orow + (size_t)n * p.out.pitch;
-                        if (GRAY) {  // channels (y, alpha) -> (y, y, y, alpha)
-                            *reinterpret_cast<uint32_t *>(px) = q[0] * 0x010101u | (q[NCH - 1] << 24);
-                        } else {     // two of the four bytes
-                            *reinterpret_cast<uint16_t *>(px + C0) = (uint16_t)(q[0] | (q[NCH - 1] << 8));
-                        }
-                    }
-                }
-            }
+            if (active)
+                v_pass_batch<C, R, GRAY, C0, NCH>(p, Hb_base + slot * kHbFloats + bcol, b, NB, bx < W, orow, vacc2, vaccl);
             __threadfence_block();
             bar_arrive(kB2Empty0 + slot, kParties);
         }
@@ -183,8 +205,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
     const size_t total = (size_t)items_per_frame * p.in.frames;
     uint32_t g = 0;  // running batch counter: buffer slot = g & 1, identical sequence in all groups
     // threads meeting at the H-plane barriers: A + B, plus C when it shares the blur-only V pass (RGBA)
-    constexpr int kNCons = (MODE == 1 && !GRAY) ? 2 : 1;
-    constexpr int kABParties = (1 + kNCons) * kC2Group;
+    constexpr int kABParties = (C::HGROUPS + C::VGROUPS) * kC2Group;  // producing + consuming groups
 
 // per-item geometry, identical in the three groups
 #define C2_ITEM_GEOMETRY()                                                                              \
@@ -199,21 +220,23 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
     const int nbatch = (Q + C::RB - 1) / C::RB;                                                         \
     (void)x0, (void)NB
 
-    if (tid < kC2Group) {
-        // =========================== group A: staging + H pass ===========================
-        // blur-only mode: group C idles on the 24-register minimum and group A (4 channels) takes its share
-        if constexpr (MODE == 1 && GRAY) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(88));
-        else if constexpr (MODE == 1) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(64));
-        else asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(NORM_C2_REGS_A));
+    // =========================== group A (and C in MODE 1): staging + H pass ===========================
+    // ROLE 0 = group A: channels [0, CH_A).  ROLE 1 = group C in MODE 1 after grayscale: the alpha channel.
+    auto h_group = [&](auto role_tag) {
+        constexpr int ROLE = decltype(role_tag)::value;
+        constexpr int c0 = ROLE == 0 ? 0 : C::CH - 1;
+        constexpr int NCHH = ROLE == 0 ? C::CH_A : 1;
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(C::REGS_H));
+        constexpr int kHT = C::HTHREADS;
+        const int hid = tid < kC2Group ? tid : tid - kC2Group;  // index within the H-pass threads
         constexpr int NC4 = C::SRCW / 4;           // 16-byte chunks per staged row
-        constexpr int NRG = kC2Group / NC4;        // staging row groups (threads beyond NRG*NC4 idle)
-        const int st_c4 = tid % NC4, st_rg = tid / NC4;
+        constexpr int NRG = kHT / NC4;             // staging row groups (threads beyond NRG*NC4 idle)
+        const int st_c4 = hid % NC4, st_rg = hid / NC4;
 
         for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
             C2_ITEM_GEOMETRY();
             const uint8_t *in_frame = p.in.ptr + (size_t)f * p.in.frame_stride;
             const uint32_t pitch32 = (uint32_t)p.in.pitch;
-
             // cp.async one batch of source rows (ClampToEdge in x and y) into staging buffer `buf`.
             // Everything but the frame base is recomputed here so that nothing stays live (or gets
             // spilled) across the H pass; the row loop is unrolled and costs a clamp, one 32x32+64
@@ -253,13 +276,13 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                 asm volatile("cp.async.commit_group;" ::: "memory");
             };
 
-            bar_sync(kB2A, kC2Group);  // previous item's last H pass is done with the staging buffers
+            bar_sync(kB2A, kHT);  // previous item's last H pass is done with the staging buffers
             stage_issue(0, 0);
 
             for (int b = 0; b < nbatch; ++b, ++g) {
                 uint32_t *stg = stg_base + (b & 1) * (C::RB * C::STG_STRIDE);
                 asm volatile("cp.async.wait_group 0;" ::: "memory");
-                bar_sync(kB2A, kC2Group);
+                bar_sync(kB2A, kHT);
                 if (b + 1 < nbatch) stage_issue(b + 1, (b + 1) & 1);
                 if (FRONT) {
                     if (st_rg < NRG) {
@@ -281,59 +304,62 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                             *cell = v;
                         }
                     }
-                    bar_sync(kB2A, kC2Group);
+                    bar_sync(kB2A, kHT);
                 }
 
                 const int slot = (int)(g & 1u);
-                bar_sync(kB2Empty0 + slot, kABParties);  // the consumer group(s) released this H-plane slot
-                for (int it = tid; it < C::RB * C::SEGS; it += kC2Group) {
-                    const int seg = it % C::SEGS, j = it / C::SEGS;
-                    const uint32_t *sp = stg + j * C::STG_STRIDE + C::OFF0 + seg * C::T;
-                    constexpr int TP = C::T / 2;
-                    float2 acc2[TP][C::CH];
+                bar_sync(kB2Empty0 + slot, kABParties);  // the consuming group(s) released this H-plane slot
+                // one thread = (row, segment) of the channels [c0, c0 + NCHH)
+                {
+                    for (int it = hid & (kC2Group - 1); it < C::RB * C::SEGS; it += kC2Group) {
+                        const int seg = it % C::SEGS, j = it / C::SEGS;
+                        const uint32_t *sp = stg + j * C::STG_STRIDE + C::OFF0 + seg * C::T;
+                        constexpr int TP = C::T / 2;
+                        float2 acc2[TP][NCHH];
 #pragma unroll
-                    for (int i = 0; i < TP; ++i)
+                        for (int i = 0; i < TP; ++i)
 #pragma unroll
-                        for (int c = 0; c < C::CH; ++c) acc2[i][c] = make_float2(0.0f, 0.0f);
+                            for (int c = 0; c < NCHH; ++c) acc2[i][c] = make_float2(0.0f, 0.0f);
 #pragma unroll
-                    for (int jj = 0; jj < C::T + R - 1; ++jj) {
-                        const uint32_t px = sp[jj];
-                        float cv[C::CH];
+                        for (int jj = 0; jj < C::T + R - 1; ++jj) {
+                            const uint32_t px = sp[jj];
+                            float cv[NCHH];
 #pragma unroll
-                        for (int c = 0; c < C::CH; ++c) cv[c] = byte_f(px, C::chan_byte(c));
+                            for (int c = 0; c < NCHH; ++c) cv[c] = byte_f(px, C::chan_byte(c0 + c));
 #pragma unroll
-                        for (int i = 0; i < TP; ++i) {
-                            const int k = jj - 2 * i;  // tap of output 2i; output 2i+1 takes k-1 (a zero tap adds exactly 0)
-                            if (k >= 0 && k <= R) {
+                            for (int i = 0; i < TP; ++i) {
+                                const int k = jj - 2 * i;  // tap of output 2i; output 2i+1 takes k-1 (a zero tap adds exactly 0)
+                                if (k >= 0 && k <= R) {
 #pragma unroll
-                                for (int c = 0; c < C::CH; ++c)
-                                    acc2[i][c] = __ffma2_rn(p.tp[k], make_float2(cv[c], cv[c]), acc2[i][c]);
+                                    for (int c = 0; c < NCHH; ++c)
+                                        acc2[i][c] = __ffma2_rn(p.tp[k], make_float2(cv[c], cv[c]), acc2[i][c]);
+                                }
                             }
                         }
+                        float *hp = Hb_base + slot * kHbFloats + j * C::HS + seg * C::T;
+#pragma unroll
+                        for (int c = 0; c < NCHH; ++c)
+#pragma unroll
+                            for (int i = 0; i < TP; i += 2)
+                                if (seg * C::T + 2 * i < C::HS)  // columns beyond the stored width are dropped
+                                    *reinterpret_cast<float4 *>(hp + (c0 + c) * (C::RB * C::HS) + 2 * i) =
+                                            make_float4(acc2[i][c].x, acc2[i][c].y, acc2[i + 1][c].x, acc2[i + 1][c].y);
                     }
-                    float *hp = Hb_base + slot * kHbFloats + j * C::HS + seg * C::T;
-#pragma unroll
-                    for (int c = 0; c < C::CH; ++c)
-#pragma unroll
-                        for (int i = 0; i < TP; i += 2)
-                            if (seg * C::T + 2 * i < C::HS)  // columns beyond the stored width are dropped
-                                *reinterpret_cast<float4 *>(hp + c * (C::RB * C::HS) + 2 * i) =
-                                        make_float4(acc2[i][c].x, acc2[i][c].y, acc2[i + 1][c].x, acc2[i + 1][c].y);
                 }
                 __threadfence_block();
                 bar_arrive(kB2Full0 + slot, kABParties);
             }
         }
+    };
+    if (tid < kC2Group) {
+        h_group(std::integral_constant<int, 0>{});
+    } else if (C::HGROUPS == 2 && tid >= 2 * kC2Group) {
+        h_group(std::integral_constant<int, 1>{});
     } else if (tid < 2 * kC2Group) {
         // =========================== group B: V pass + quantise + intensity ===========================
         if constexpr (MODE == 1) {
-            if constexpr (GRAY) {
-                asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(128));
-                blur_only_consumer<C, R, true, 0, 2, 1>(p, Hb_base, tid - kC2Group, items_per_frame, total);
-            } else {
-                asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(88));
-                blur_only_consumer<C, R, false, 0, 2, 2>(p, Hb_base, tid - kC2Group, items_per_frame, total);
-            }
+            asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REGS_V));
+            blur_only_consumer<C, R, GRAY, 0, 2, kABParties>(p, Hb_base, tid - kC2Group, items_per_frame, total);
             return;
         }
         asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(NORM_C2_REGS_B));
@@ -406,13 +432,9 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         }
     } else {
         // =========================== group C: Sobel + store + SSIM ===========================
-        if constexpr (MODE == 1) {
-            if constexpr (GRAY) {
-                asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(24));  // idle: hand the registers over
-            } else {
-                asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(88));
-                blur_only_consumer<C, R, false, 2, 2, 2>(p, Hb_base, tid - 2 * kC2Group, items_per_frame, total);
-            }
+        if constexpr (MODE == 1) {  // RGBA blur: the V pass of channels 2 and 3 (after grayscale group C never gets here)
+            asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REGS_V));
+            blur_only_consumer<C, R, GRAY, 2, 2, kABParties>(p, Hb_base, tid - 2 * kC2Group, items_per_frame, total);
             return;
         }
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(NORM_C2_REGS_C));

@@ -8,3 +8,7 @@ for r in 21 7 3; do
 done
 python tools/prof_chain.py --frames 256 --reps 5 --gray 1 --lib tools/ab/base.so | sed 's/^/base /'
 python tools/prof_chain.py --frames 256 --reps 5 --gray 1 | sed 's/^/new  /'
+for extra in "--radius 21" "--radius 7" "--radius 21 --gray 1"; do
+  python tools/prof_chain.py --frames 256 --reps 5 --blur-only $extra --lib tools/ab/base.so | sed 's/^/base /'
+  python tools/prof_chain.py --frames 256 --reps 5 --blur-only $extra | sed 's/^/new  /'
+done

@@ -17,6 +17,7 @@ ap.add_argument("--width", type=int, default=1920)
 ap.add_argument("--height", type=int, default=1080)
 ap.add_argument("--gray", type=int, default=0)
 ap.add_argument("--no-ssim", action="store_true")
+ap.add_argument("--blur-only", action="store_true", help="time norm_cuda_blur (all four channels) instead of the chain")
 ap.add_argument("--lib", default=None, help="alternative libnorm_cuda.so (A/B runs)")
 a = ap.parse_args()
 if a.lib:
@@ -31,11 +32,17 @@ src = ctx.image_wrap(src_t.data_ptr(), W, H, n, W * 4, W * 4 * H)
 dst = ctx.image_wrap(dst_t.data_ptr(), W, H, n, W * 4, W * 4 * H)
 f = nb.FeatureUniform(W, H)
 f.raw.blur, f.raw.blur_radius, f.raw.edge_detect, f.raw.grayscale = 1, a.radius, 1, a.gray
-ctx.chain_async(f, src, dst, nb.NORM_CS_RAW, None if a.no_ssim else ss.data_ptr())
+if a.blur_only:
+    f.raw.edge_detect = 0
+    run = lambda: ctx.effects(f, src, dst, nb.NORM_CS_RAW)
+else:
+    run = lambda: ctx.chain_async(f, src, dst, nb.NORM_CS_RAW, None if a.no_ssim else ss.data_ptr())
+run()
 ctx.sync()
 ctx.timer_start()
 for _ in range(a.reps):
-    ctx.chain_async(f, src, dst, nb.NORM_CS_RAW, None if a.no_ssim else ss.data_ptr())
+    run()
 ctx.timer_stop()
 ms = ctx.timer_elapsed_ms() / a.reps
-print(f"r={a.radius} gray={a.gray} {n}x{W}x{H}: {ms:.3f} ms/pass  {n*W*H/ms/1e6:.1f} Gpx/s  {n*W*H*8/ms/1e6:.0f} GB/s algorithmic")
+what = "blur-only" if a.blur_only else "chain"
+print(f"{what} r={a.radius} gray={a.gray} {n}x{W}x{H}: {ms:.3f} ms/pass  {n*W*H/ms/1e6:.1f} Gpx/s  {n*W*H*8/ms/1e6:.0f} GB/s algorithmic")

@@ -47,6 +47,15 @@ timeit("front: invert", lambda: ctx.front(f2, src, dst, nb.NORM_CS_RAW), 8)
 timeit("sobel", lambda: ctx.sobel(src, dst), 8)
 timeit("sharpen", lambda: ctx.sharpen(16, src, dst), 8)
 timeit("ssim (two images)", lambda: ctx.ssim(src, dst), 8)
+timeit("box blur 3x3", lambda: ctx.box_blur(src, dst), 8)
+rng = np.random.default_rng(2)
+circles = [nb.Circle((float(rng.uniform(0, 1)), float(rng.uniform(0, 1))), float(rng.uniform(0.005, 0.05))) for _ in range(64)]
+draw = nb.DrawUniform()
+draw.toggle_crosshair(), draw.set_circle_center(960.0, 540.0), draw.set_circle_radius(25.0)
+timeit("overlay: no shapes (copy)", lambda: ctx.overlay(src, dst, []), 8)
+timeit("overlay: 64 circles + crosshair", lambda: ctx.overlay(src, dst, circles, 5, draw), 8)
+big = [nb.Circle((0.5, 0.5), 0.45)] + circles
+timeit("overlay: + one circle over 1/3 frame", lambda: ctx.overlay(src, dst, big, 0, draw), 8)
 for r in (3, 7, 21):
     timeit(f"blur r={r} (RGBA, 4 channels)", lambda: ctx.blur(r, src, dst), 8)
 # expansion: one 7680x4320 image per call, RGB8 -> RGBA8 (7 B/px) and 1-bit gray (4.125 B/px); includes the H2D of the packed scanlines
