@@ -39,8 +39,8 @@ static_assert(NORM_C2_REGS_A + NORM_C2_REGS_B + NORM_C2_REGS_C == 240, "register
 // MODE 0: front -> blur -> Sobel (+ SSIM)   one blurred channel triple -> intensity -> group C
 // MODE 1: front -> blur                     all four channels are blurred (image_shader.wgsl:88-103 blurs
 //         alpha too); after grayscale the three colour channels coincide, so two distinct channels (y, a)
-//         remain.  The H pass is the larger half of the work here, so groups A and C both run it (half of
-//         the channels each, staging shared) and group B runs the V pass for all channels and stores RGBA8
+//         remain: groups A and C both run the H pass (one channel each, staging shared) and group B the V
+//         pass of both.  On RGBA group A runs the H pass of all four channels, B and C the V pass of two each.
 template <int R, bool GRAY, int MODE = 0>
 struct Fused2Cfg {
     static_assert(R % 2 == 1, "odd radii");
