@@ -20,6 +20,7 @@
 #include "common.cuh"
 #include "filter_kernels.cuh"
 #include "overlay_kernels.cuh"
+#include "stencil_kernels.cuh"
 #include "stage_kernels.cuh"
 #include "unfilter_kernels.cuh"
 
@@ -261,28 +262,35 @@ norm_status launch_blur(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const 
     }
 }
 
-norm_status launch_sobel(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const ImgView &out) {
-    const uint32_t tx = (in.w + kSobW - 1) / kSobW, ty = (in.h + kSobH - 1) / kSobH;
-    const unsigned grid = grid_for(ctx, (size_t)tx * ty * in.frames, 8);
-    sobel_kernel<<<grid, 256, 0, s>>>(in, out, tx, ty);
+// 3x3 stencils on a register window (stencil_kernels.cuh), optionally with the front stage applied at load
+template <int OP>
+norm_status launch_stencil3(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const ImgView &out, const Lut256 *lut,
+                            bool use_lut, bool gray, bool inv, int factor) {
+    const uint32_t tx = (in.w + kS3Cols - 1) / kS3Cols, ty = (in.h + kS3Rows - 1) / kS3Rows;
+    const unsigned grid = grid_for(ctx, ((size_t)tx * ty * in.frames + 7) / 8, 8);
+    static const Lut256 none{};
+    const Lut256 &l = lut ? *lut : none;
+    const uint32_t inv_mask = inv ? 0x00ffffffu : 0u;
+    switch ((use_lut ? 1 : 0) | (gray ? 2 : 0)) {
+    case 0: stencil3_kernel<OP, 0><<<grid, 256, 0, s>>>(in, out, l, inv_mask, factor, tx, ty); break;
+    case 1: stencil3_kernel<OP, 1><<<grid, 256, 0, s>>>(in, out, l, inv_mask, factor, tx, ty); break;
+    case 2: stencil3_kernel<OP, 2><<<grid, 256, 0, s>>>(in, out, l, inv_mask, factor, tx, ty); break;
+    default: stencil3_kernel<OP, 3><<<grid, 256, 0, s>>>(in, out, l, inv_mask, factor, tx, ty); break;
+    }
     LAUNCH_CHECK(ctx);
     return NORM_OK;
+}
+
+norm_status launch_sobel(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const ImgView &out) {
+    return launch_stencil3<kOpSobel>(ctx, s, in, out, nullptr, false, false, false, 0);
 }
 
 norm_status launch_sharpen(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const ImgView &out, uint32_t factor) {
-    const uint32_t tx = (in.w + kStW - 1) / kStW, ty = (in.h + kStH - 1) / kStH;
-    const unsigned grid = grid_for(ctx, (size_t)tx * ty * in.frames, 8);
-    sharpen_kernel<<<grid, 256, 0, s>>>(in, out, (int)factor, tx, ty);
-    LAUNCH_CHECK(ctx);
-    return NORM_OK;
+    return launch_stencil3<kOpSharpen>(ctx, s, in, out, nullptr, false, false, false, (int)factor);
 }
 
 norm_status launch_box_blur(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const ImgView &out) {
-    const uint32_t tx = (in.w + kStW - 1) / kStW, ty = (in.h + kStH - 1) / kStH;
-    const unsigned grid = grid_for(ctx, (size_t)tx * ty * in.frames, 8);
-    box_blur_kernel<<<grid, 256, 0, s>>>(in, out, tx, ty);
-    LAUNCH_CHECK(ctx);
-    return NORM_OK;
+    return launch_stencil3<kOpBox>(ctx, s, in, out, nullptr, false, false, false, 0);
 }
 
 // sRGB encode thresholds / decode values of the shape render texture (host, double -> f32)
@@ -365,6 +373,11 @@ norm_status run_stages_unfused(norm_ctx *ctx, Slot &slot, const StagePlan &p, co
         bool fused = false;  // front -> blur as one pipelined kernel where it is instantiated
         NORM_TRY(try_launch_blur_fused(ctx, slot, p, in, out, &fused));
         if (fused) return NORM_OK;
+    }
+    if (n == 2 && p.front && (p.edge != p.sharpen)) {
+        // the reference frame "compute chain -> edge or sharpen": front applied at load, one pass over HBM
+        if (p.edge) return launch_stencil3<kOpSobel>(ctx, slot.stream, in, out, &p.lut, p.use_lut, p.gray, p.inv, 0);
+        return launch_stencil3<kOpSharpen>(ctx, slot.stream, in, out, &p.lut, p.use_lut, p.gray, p.inv, (int)p.factor);
     }
     const size_t frame_bytes = align_up((size_t)in.w * 4, 256) * in.h;
     uint32_t chunk = in.frames;

@@ -10,6 +10,8 @@ import numpy as np
 import torch
 import norm_b200 as nb
 
+if os.environ.get("NORM_LIB"):  # A/B against another build of the library
+    nb._lib.LIB_PATH = os.path.abspath(os.environ["NORM_LIB"])
 W, H, n = 1920, 1080, int(os.environ.get("FRAMES", 256))
 peak = 6555.5
 try:
@@ -47,6 +49,14 @@ timeit("front: invert", lambda: ctx.front(f2, src, dst, nb.NORM_CS_RAW), 8)
 timeit("sobel", lambda: ctx.sobel(src, dst), 8)
 timeit("sharpen", lambda: ctx.sharpen(16, src, dst), 8)
 timeit("ssim (two images)", lambda: ctx.ssim(src, dst), 8)
+fe = nb.FeatureUniform(W, H)
+fe.raw.edge_detect = 1
+timeit("effects: sRGB table + edge (1 frame pass)", lambda: ctx.effects(fe, src, dst, nb.NORM_CS_REFERENCE), 8)
+fe.raw.grayscale = 1
+timeit("effects: sRGB + gray + edge", lambda: ctx.effects(fe, src, dst, nb.NORM_CS_REFERENCE), 8)
+fs = nb.FeatureUniform(W, H)
+fs.raw.sharpen = 1
+timeit("effects: sRGB table + sharpen", lambda: ctx.effects(fs, src, dst, nb.NORM_CS_REFERENCE), 8)
 timeit("box blur 3x3", lambda: ctx.box_blur(src, dst), 8)
 rng = np.random.default_rng(2)
 circles = [nb.Circle((float(rng.uniform(0, 1)), float(rng.uniform(0, 1))), float(rng.uniform(0.005, 0.05))) for _ in range(64)]
