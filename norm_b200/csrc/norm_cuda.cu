@@ -258,6 +258,15 @@ norm_status launch_blur(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const 
     case 7: return launch_blur_r<7>(ctx, s, in, out, taps);
     case 21: return launch_blur_r<21>(ctx, s, in, out, taps);
     case 39: return launch_blur_r<39>(ctx, s, in, out, taps);
+    // RGBA blur above r = 21 has no pipelined kernel (4 x R running outputs): give the UI's radii the unrolled tile kernel
+    case 23: return launch_blur_r<23>(ctx, s, in, out, taps);
+    case 25: return launch_blur_r<25>(ctx, s, in, out, taps);
+    case 27: return launch_blur_r<27>(ctx, s, in, out, taps);
+    case 29: return launch_blur_r<29>(ctx, s, in, out, taps);
+    case 31: return launch_blur_r<31>(ctx, s, in, out, taps);
+    case 33: return launch_blur_r<33>(ctx, s, in, out, taps);
+    case 35: return launch_blur_r<35>(ctx, s, in, out, taps);
+    case 37: return launch_blur_r<37>(ctx, s, in, out, taps);
     default: return launch_blur_r<0>(ctx, s, in, out, taps);
     }
 }
@@ -490,6 +499,32 @@ norm_status launch_fused_r(norm_ctx *ctx, Slot &slot, const StagePlan &p, const 
     return launch_fused<R, false, false, 1>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
 }
 
+// The other radii the reference's UI can reach (odd, 3..39 in steps of 2, feature_uniform.rs:66-84): pipelined
+// kernel only (the first-generation kernel is not instantiated for them, except on RGB above r = 21 where the
+// pipelined kernel's 3 x R running outputs do not fit).
+template <int R>
+norm_status launch_fused_rx(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
+                            double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1, bool *fused) {
+    if (p.gray) return launch_fused<R, true, true, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+    if constexpr (R <= 21) {
+        if (ctx->fused_gen == 1) {
+            *fused = false;
+            return NORM_OK;
+        }
+        if (p.front) return launch_fused<R, false, true, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+        return launch_fused<R, false, false, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+    } else {
+        if (p.front) return launch_fused<R, false, true, 1>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+        return launch_fused<R, false, false, 1>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+    }
+}
+
+#ifdef NORM_NO_EXTRA_RADII  // development builds: only the BASELINE radii (3, 7, 21, 39); a third of the compile time
+#define NORM_EXTRA_RADII(X)
+#else
+#define NORM_EXTRA_RADII(X) X(5) X(9) X(11) X(13) X(15) X(17) X(19) X(23) X(25) X(27) X(29) X(31) X(33) X(35) X(37)
+#endif
+
 // front -> blur with nothing after it (norm_cuda_blur, the blur effect of norm_cuda_effects, blur-only chains):
 // pipelined kernel in MODE 1.  CH*R accumulators per thread: R <= 21 on RGBA (4 channels), any R after grayscale (2).
 template <int R>
@@ -514,6 +549,9 @@ norm_status try_launch_blur_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p,
     case 7: return launch_blur_only_r<7>(ctx, slot, p, in, out, fused);
     case 21: return launch_blur_only_r<21>(ctx, slot, p, in, out, fused);
     case 39: return launch_blur_only_r<39>(ctx, slot, p, in, out, fused);
+#define X(R_) case R_: return launch_blur_only_r<R_>(ctx, slot, p, in, out, fused);
+        NORM_EXTRA_RADII(X)
+#undef X
     default: return NORM_OK;
     }
 }
@@ -529,6 +567,9 @@ norm_status try_launch_chain_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p
     case 7: return launch_fused_r<7>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
     case 21: return launch_fused_r<21>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
     case 39: return launch_fused_r<39>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+#define X(R_) case R_: return launch_fused_rx<R_>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1, fused);
+        NORM_EXTRA_RADII(X)
+#undef X
     default: *fused = false; return NORM_OK;
     }
 }

@@ -471,3 +471,23 @@ def test_effects_flips(ctx, oracle):
                 of = oracle_uniform(oracle, f)
                 of.transform[0][0], of.transform[1][1] = f.raw.transform[0][0], f.raw.transform[1][1]
                 assert np.array_equal(oracle.effects(img, of, oracle.CS_RAW), exp)
+
+
+# every radius the reference's UI can reach: 3..39 in steps of 2 (feature_uniform.rs:66-84)
+@pytest.mark.parametrize("radius", list(range(3, 41, 2)))
+def test_every_ui_radius_chain_and_blur(ctx, oracle, radius):
+    w, h = 251, 97
+    img = smooth_rgba(w, h, seed=radius) if radius % 4 == 1 else splitmix_rgba(w, h, seed=radius)
+    for kw in (dict(blur=1, blur_radius=radius, edge_detect=1), dict(grayscale=1, blur=1, blur_radius=radius, edge_detect=1),
+               dict(gamma=45455, blur=1, blur_radius=radius, edge_detect=1)):
+        f = uniform(w, h, **kw)
+        src, dst = ctx.image_from_host(img), ctx.image_create(w, h, 1)
+        ssim = ctx.chain(f, src, dst, nb.NORM_CS_REFERENCE)
+        exp, es = oracle.chain_batch(img[None], oracle_uniform(oracle, f), nb.NORM_CS_REFERENCE)
+        assert np.array_equal(dst.download(), exp), (radius, kw)
+        assert abs(ssim[0] - es[0]) <= SSIM_TIGHT, (radius, kw)
+        src.destroy(), dst.destroy()
+    for kw in (dict(blur=1, blur_radius=radius), dict(grayscale=1, blur=1, blur_radius=radius)):
+        f = uniform(w, h, **kw)
+        got = run_stage(ctx, lambda s, d: ctx.effects(f, s, d, nb.NORM_CS_RAW), img)[0]
+        assert np.array_equal(got, oracle.effects(img, oracle_uniform(oracle, f), nb.NORM_CS_RAW)), (radius, kw)
