@@ -55,7 +55,10 @@ struct Fused2Cfg {
     static constexpr int OFF0 = HL - HALO - M;          // staged column of blurred column 0's first tap
     static constexpr int SRCW = (OFF0 + HS + R - 1 + 3) / 4 * 4;
     static constexpr int STG_STRIDE = SRCW;             // words, multiple of 4
-    static constexpr int RB = R * ((16 + R - 1) / R);   // rows per batch, multiple of R
+    // rows per batch: a multiple of R, about 16.  The RGBA blur (four H planes) takes R itself from R = 13 on:
+    // two times 13 or 15 rows would push its shared memory past half an SM and cost the second resident CTA
+    // (measured: +11 % / +19 % at r = 13 / 15; the chain variants are faster with the longer batch).
+    static constexpr int RB = (R >= 13 && MODE == 1 && !GRAY) ? R : R * ((16 + R - 1) / R);
     static constexpr int CH = MODE == 0 ? (GRAY ? 1 : 3) : (GRAY ? 2 : 4);
     // MODE 1 after grayscale (channels y, alpha): groups A and C both run the H pass (one channel each, staging
     // shared) and group B runs the V pass of both and stores RGBA8.  MODE 1 on RGBA: group A runs the H pass
