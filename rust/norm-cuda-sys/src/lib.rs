@@ -51,6 +51,51 @@ pub struct NormPngDesc {
     pub n_trns: i32,
 }
 
+/// The inflated IDAT stream as `ScanlineReader::new` receives it (src/png/scanline_reader.rs:15-28).
+#[repr(C)]
+pub struct NormInflatedDesc {
+    pub width: u32,
+    pub height: u32,
+    pub bit_depth: u8,
+    pub color_type: u8,
+    pub interlace: u8,
+    pub _reserved: u8,
+    pub data: *const u8,
+    pub len: usize,
+}
+
+/// src/renderer/shape_uniform.rs:3-10
+#[repr(C)]
+#[derive(Clone, Copy, Debug, Default)]
+pub struct NormShapeUniform {
+    pub width: u32,
+    pub height: u32,
+    pub num_circles: u32,
+    pub selected_circle: u32,
+}
+
+/// src/renderer/shape_uniform.rs:38-45
+#[repr(C)]
+#[derive(Clone, Copy, Debug, Default)]
+pub struct NormCircleData {
+    pub x: f32,
+    pub y: f32,
+    pub radius: f32,
+    pub _padding: f32,
+}
+
+/// src/renderer/draw_uniform.rs:3-9
+#[repr(C)]
+#[derive(Clone, Copy, Debug, Default)]
+pub struct NormDrawUniform {
+    pub crosshair: u32,
+    pub circle_center_x: f32,
+    pub circle_center_y: f32,
+    pub circle_radius: f32,
+    pub camera_view_proj: [[f32; 4]; 4],
+}
+const _: () = assert!(std::mem::size_of::<NormDrawUniform>() == 80);
+
 extern "C" {
     pub fn norm_cuda_abi_version() -> i32;
     pub fn norm_cuda_create(device: i32, out: *mut *mut norm_ctx) -> norm_status;
@@ -69,6 +114,13 @@ extern "C" {
     pub fn norm_cuda_ssim(ctx: *mut norm_ctx, a: *const norm_img, b: *const norm_img, ssim: *mut f64) -> norm_status;
     pub fn norm_cuda_ssim_moments(ctx: *mut norm_ctx, a: *const norm_img, b: *const norm_img, moments: *mut f64) -> norm_status;
     pub fn norm_ssim_from_moments(moments: *const f64, npix: f64) -> f64;
+    pub fn norm_cuda_unfilter(ctx: *mut norm_ctx, inflated: *const NormInflatedDesc, pixel_buffer: *mut u8) -> norm_status;
+    pub fn norm_cuda_unfilter_expand_rgba8(ctx: *mut norm_ctx, inflated: *const NormInflatedDesc, plte: *const u8, n_plte: i32, trns: *const u8, n_trns: i32, mode: i32, out: *mut norm_img, frame: u32) -> norm_status;
+    pub fn norm_cuda_unfilter_expand_rgba8_batch(ctx: *mut norm_ctx, inflated: *const NormInflatedDesc, n: u32, plte: *const u8, n_plte: i32, trns: *const u8, n_trns: i32, mode: i32, out: *mut norm_img, frame0: u32) -> norm_status;
+    pub fn norm_cuda_filter_scanlines(ctx: *mut norm_ctx, width: u32, height: u32, bit_depth: u8, color_type: u8, pixel_buffer: *const u8, paeth_compat: i32, stream: *mut u8, filter_types: *mut u8) -> norm_status;
+    pub fn norm_cuda_filter_image(ctx: *mut norm_ctx, img: *const norm_img, frame: u32, paeth_compat: i32, stream: *mut u8, filter_types: *mut u8) -> norm_status;
+    pub fn norm_cuda_box_blur(ctx: *mut norm_ctx, input: *const norm_img, out: *mut norm_img) -> norm_status;
+    pub fn norm_cuda_overlay(ctx: *mut norm_ctx, shapes: *const NormShapeUniform, circles: *const NormCircleData, draw: *const NormDrawUniform, input: *const norm_img, out: *mut norm_img) -> norm_status;
     pub fn norm_cuda_ssim_static(a: *const c_void, b: *const c_void, w: u32, h: u32, frames: u32, pitch: usize, frame_stride: usize, ssim_dev: *mut f64, moments_dev: *mut f64, stream: *mut c_void) -> norm_status;
 }
 
