@@ -76,7 +76,10 @@ struct Fused2Cfg {
     static constexpr int IS = 128;                      // intensity row stride
     static constexpr size_t kStgBytes = (size_t)RB * STG_STRIDE * 4;
     static constexpr size_t kHbBytes = (size_t)CH * RB * HS * 4;
-    static constexpr size_t kIstBytes = (size_t)RB * IS * 4;
+    // intensity rows exist only when Sobel follows.  Exception, measured: the RGBA blur at r = 19 / 21 keeps the
+    // allocation as padding so that ONE CTA stays resident -- its V-pass groups spill (2 x R running outputs in 88
+    // registers) and two CTAs' spill traffic costs more than the second CTA brings (64.8 vs 80.5 Gpixel/s at r = 21).
+    static constexpr size_t kIstBytes = (MODE == 0 || (!GRAY && R >= 19)) ? (size_t)RB * IS * 4 : 0;
     // + 64 words of slack: the last H segment's unused outputs read a few words past a staged row
     static constexpr size_t kSmem = 2 * kStgBytes + 256 + 2 * kHbBytes + 2 * kIstBytes + 256 * 4 * 2 + 256;
     static_assert(T % 4 == 0 && HS % 4 == 0, "16-byte H stores");
