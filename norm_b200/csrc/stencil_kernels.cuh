@@ -117,7 +117,7 @@ __device__ __forceinline__ uint32_t s3_apply(const S3Elem<OP> (&top)[6], const S
 }
 
 template <int OP, int FR>
-__global__ void __launch_bounds__(256, 3) stencil3_kernel(ImgView in, ImgView out, const __grid_constant__ Lut256 lut,
+__global__ void __launch_bounds__(256, 4) stencil3_kernel(ImgView in, ImgView out, const __grid_constant__ Lut256 lut,
                                                        uint32_t inv_mask, int factor, uint32_t tiles_x, uint32_t tiles_y) {
     __shared__ uint8_t slut[256];
     if (FR & 1) {
