@@ -20,6 +20,9 @@ NVCC_FLAGS = [
     "-Xptxas", "-v",
     "-shared", "-cudart", "static",
 ]
+# Development builds: NORM_NVCC_EXTRA="--split-compile 0 -DNORM_NO_EXTRA_RADII" compiles in about 30 s instead of
+# 3.4 min.  Not the default: --split-compile changes register allocation in a few kernels (measured: grayscale
+# chain r=21 158 -> 148 Gpixel/s, RGBA blur r=21 80 -> 75); results stay bit-exact either way.
 
 
 def _stale(target, sources):
