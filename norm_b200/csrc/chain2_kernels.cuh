@@ -29,6 +29,10 @@ constexpr int kC2Group = 128, kC2Threads = 3 * kC2Group;
 #ifndef NORM_C2_T
 #define NORM_C2_T 12
 #endif
+#ifndef NORM_C2_REGS_H4
+#define NORM_C2_REGS_H4 64  // RGBA blur: group A (H pass of four channels); groups B and C share the rest
+#define NORM_C2_T4 8        // and its H-pass outputs per thread above r = 9
+#endif
 #ifndef NORM_C2_REGS_A
 #define NORM_C2_REGS_A 56
 #define NORM_C2_REGS_B 128
@@ -48,7 +52,7 @@ struct Fused2Cfg {
     static constexpr int HALO = MODE == 0 ? 1 : 0;      // Sobel needs one blurred pixel around each output
     static constexpr int SW = 120;                      // output columns per strip
     static constexpr int BW = SW + 2 * HALO;            // blurred / intensity columns
-    static constexpr int T = (MODE == 1 && !GRAY && R > 9) ? 8 : NORM_C2_T;  // H-pass outputs per thread (4-channel H pass: fewer, for registers)
+    static constexpr int T = (MODE == 1 && !GRAY && R > 9) ? NORM_C2_T4 : NORM_C2_T;  // H-pass outputs per thread (4-channel H pass: fewer, for registers)
     static constexpr int SEGS = (BW + T - 1) / T;       // 11
     static constexpr int HS = (BW + 3) / 4 * 4;         // 124: H plane row stride = columns actually stored
     static constexpr int HL = ((M + HALO) + 3) / 4 * 4; // staged left halo, 16-byte chunks
@@ -69,17 +73,14 @@ struct Fused2Cfg {
     static constexpr int CH_A = (MODE == 1 && GRAY) ? 1 : CH;   // channels of group A's H pass (from 0)
     static constexpr int HTHREADS = HGROUPS * 128;
     // register budgets (setmaxnreg), summing to 3 x 80
-    static constexpr int REGS_H = (MODE == 1 && !GRAY) ? 64 : NORM_C2_REGS_A;
-    static constexpr int REGS_V = (MODE == 1 && !GRAY) ? 88 : NORM_C2_REGS_B;
+    static constexpr int REGS_H = (MODE == 1 && !GRAY) ? NORM_C2_REGS_H4 : NORM_C2_REGS_A;
+    static constexpr int REGS_V = (MODE == 1 && !GRAY) ? (240 - NORM_C2_REGS_H4) / 2 : NORM_C2_REGS_B;
     // source byte of channel c: MODE 1 + GRAY blurs (y, alpha) = bytes (0, 3)
     __host__ __device__ static constexpr int chan_byte(int c) { return (MODE == 1 && GRAY && c == 1) ? 3 : c; }
     static constexpr int IS = 128;                      // intensity row stride
     static constexpr size_t kStgBytes = (size_t)RB * STG_STRIDE * 4;
     static constexpr size_t kHbBytes = (size_t)CH * RB * HS * 4;
-    // intensity rows exist only when Sobel follows.  Exception, measured: the RGBA blur at r = 19 / 21 keeps the
-    // allocation as padding so that ONE CTA stays resident -- its V-pass groups spill (2 x R running outputs in 88
-    // registers) and two CTAs' spill traffic costs more than the second CTA brings (64.8 vs 80.5 Gpixel/s at r = 21).
-    static constexpr size_t kIstBytes = (MODE == 0 || (!GRAY && R >= 19)) ? (size_t)RB * IS * 4 : 0;
+    static constexpr size_t kIstBytes = MODE == 0 ? (size_t)RB * IS * 4 : 0;  // intensity rows exist only when Sobel follows
     // + 64 words of slack: the last H segment's unused outputs read a few words past a staged row
     static constexpr size_t kSmem = 2 * kStgBytes + 256 + 2 * kHbBytes + 2 * kIstBytes + 256 * 4 * 2 + 256;
     static_assert(T % 4 == 0 && HS % 4 == 0, "16-byte H stores");
@@ -90,6 +91,14 @@ enum {
     kB2IFull0 = 5, kB2IFull1 = 6, kB2IEmpty0 = 7, kB2IEmpty1 = 8,  // B <-> C: intensity rows
     kB2A = 9, kB2C = 10
 };
+
+// stores executed under a predicate instead of a branch
+__device__ __forceinline__ void st_global_pred_u32(void *ptr, uint32_t v, bool pred) {
+    asm volatile("{ .reg .pred p; setp.ne.u32 p, %0, 0; @p st.global.u32 [%1], %2; }" ::"r"((uint32_t)pred), "l"(ptr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_global_pred_u16(void *ptr, uint32_t v, bool pred) {
+    asm volatile("{ .reg .pred p; setp.ne.u32 p, %0, 0; @p st.global.u16 [%1], %2; }" ::"r"((uint32_t)pred), "l"(ptr), "h"((uint16_t)v) : "memory");
+}
 
 // V pass of one batch for channels [C0, C0+NCH) of one blurred column (MODE 1): NCH x R running outputs in
 // registers (static rotation: the row loop is fully unrolled and RB % R == 0), quantise, store those bytes
@@ -126,18 +135,15 @@ __device__ __forceinline__ void v_pass_batch(const FusedParams &p, const float *
             q[c] = __float_as_uint(__fadd_rn(o, 12582912.0f)) & 0xffu;
         }
         const int n = b * C::RB + j - (R - 1);  // output row relative to the band's first row
-        if (n >= 0 && n < NB && in_image) {
-            uint8_t *px = orow + (size_t)n * p.out.pitch;
-            if constexpr (GRAY) {  // channels (y, alpha) -> (y, y, y, alpha)
-                *reinterpret_cast<uint32_t *>(px) = q[0] * 0x010101u | (q[NCH - 1] << 24);
-            } else if constexpr (NCH == 3) {  // r, g, b; the alpha byte comes from group C
-                *reinterpret_cast<uint16_t *>(px + C0) = (uint16_t)(q[0] | (q[1] << 8));
-                px[C0 + 2] = (uint8_t)q[2];
-            } else if constexpr (NCH == 1) {
-                px[C0] = (uint8_t)q[0];
-            } else {
-                *reinterpret_cast<uint16_t *>(px + C0) = (uint16_t)(q[0] | (q[NCH - 1] << 8));
-            }
+        // predicated stores, no branch: a branch per row inside this unrolled body keeps the compiler from
+        // holding the tap pairs in uniform registers (they end up in 2 x R vector registers and spill)
+        const bool valid = n >= 0 && n < NB && in_image;
+        uint8_t *px = orow + (size_t)n * p.out.pitch;
+        if constexpr (GRAY) {  // channels (y, alpha) -> (y, y, y, alpha)
+            st_global_pred_u32(px, q[0] * 0x010101u | (q[NCH - 1] << 24), valid);
+        } else {               // two of the four bytes
+            static_assert(NCH == 2, "RGBA: two channels per V-pass thread");
+            st_global_pred_u16(px + C0, q[0] | (q[1] << 8), valid);
         }
     }
 }
