@@ -17,7 +17,7 @@
 // A->B hand over double-buffered f32 H planes, B->C double-buffered intensity rows; each
 // hand-off is a full/empty pair of named barriers per slot, so no group ever waits on more
 // than its neighbour.  Register budgets follow the roles (setmaxnreg): B holds 3*R
-// accumulators and takes 128 registers, A and C give theirs up (56 each).
+// accumulators and takes 112 registers, A keeps 72 (no spills in the H pass), C gives its share up (56).
 // Instantiated for R <= 21 on RGB (3*21 accumulators); wider radii use chain_fused_kernel.
 #pragma once
 #include "chain_kernels.cuh"
@@ -34,8 +34,8 @@ constexpr int kC2Group = 128, kC2Threads = 3 * kC2Group;
 #define NORM_C2_T4 8        // and its H-pass outputs per thread above r = 9
 #endif
 #ifndef NORM_C2_REGS_A
-#define NORM_C2_REGS_A 56
-#define NORM_C2_REGS_B 128
+#define NORM_C2_REGS_A 72   // measured best of 56/128/56, 64/112/64, 72/104/64, 72/112/56, 80/96/64, 80/104/56, 80/112/48:
+#define NORM_C2_REGS_B 112  // group A stops spilling at 72, group B's 3 x R running outputs + temporaries fit 112
 #define NORM_C2_REGS_C 56
 #endif
 static_assert(NORM_C2_REGS_A + NORM_C2_REGS_B + NORM_C2_REGS_C == 240, "register budgets must sum to 3 x 80");
@@ -73,8 +73,8 @@ struct Fused2Cfg {
     static constexpr int CH_A = (MODE == 1 && GRAY) ? 1 : CH;   // channels of group A's H pass (from 0)
     static constexpr int HTHREADS = HGROUPS * 128;
     // register budgets (setmaxnreg), summing to 3 x 80
-    static constexpr int REGS_H = (MODE == 1 && !GRAY) ? NORM_C2_REGS_H4 : NORM_C2_REGS_A;
-    static constexpr int REGS_V = (MODE == 1 && !GRAY) ? (240 - NORM_C2_REGS_H4) / 2 : NORM_C2_REGS_B;
+    static constexpr int REGS_H = MODE == 1 ? (GRAY ? 56 : NORM_C2_REGS_H4) : NORM_C2_REGS_A;              // MODE 1 + GRAY: two H groups
+    static constexpr int REGS_V = MODE == 1 ? (GRAY ? 128 : (240 - NORM_C2_REGS_H4) / 2) : NORM_C2_REGS_B;
     // source byte of channel c: MODE 1 + GRAY blurs (y, alpha) = bytes (0, 3)
     __host__ __device__ static constexpr int chan_byte(int c) { return (MODE == 1 && GRAY && c == 1) ? 3 : c; }
     static constexpr int IS = 128;                      // intensity row stride
