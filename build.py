@@ -35,15 +35,21 @@ def _stale(target, sources):
 def build_cuda(force=False, verbose=False):
     srcs = [os.path.join(CSRC, n) for n in sorted(os.listdir(CSRC)) if n != "norm_nccl.cu"]
     srcs += [os.path.join(ROOT, "include", "norm_cuda.h"), os.path.abspath(__file__)]
-    if not (force or _stale(LIB, srcs)):
-        return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     env = dict(os.environ)
     env.pop("CC", None)
     env.pop("CXX", None)
     extra = os.environ.get("NORM_NVCC_EXTRA", "").split()
     cmd = [nvcc, "-ccbin", "/usr/bin/g++"] + NVCC_FLAGS + extra + ["-o", LIB, os.path.join(CSRC, "norm_cuda.cu")]
+    # a library built with other flags (e.g. the quick development build) counts as stale
+    flags_file = LIB + ".flags"
+    same_flags = os.path.exists(flags_file) and open(flags_file).read() == " ".join(cmd)
+    if not (force or not same_flags or _stale(LIB, srcs)):
+        return LIB
     r = subprocess.run(cmd, capture_output=True, text=True, env=env)
+    if r.returncode == 0:
+        with open(flags_file, "w") as f:
+            f.write(" ".join(cmd))
     log = os.path.join(ROOT, "norm_b200", "build.log")
     with open(log, "w") as f:
         f.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
