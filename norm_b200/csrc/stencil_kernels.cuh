@@ -103,8 +103,9 @@ __device__ __forceinline__ uint32_t s3_apply(const S3Elem<OP> (&top)[6], const S
         const int v1 = k1 * (int)((c >> 8) & 0xffu) - factor * (int)(so & 0xffffu);
         const int v2 = k1 * (int)((c >> 16) & 0xffu) - factor * (int)(se >> 16);
         const int v3 = k1 * (int)(c >> 24) - factor * (int)(so >> 16);
-        return pack_rgba((uint32_t)clampi(v0, 0, 255), (uint32_t)clampi(v1, 0, 255), (uint32_t)clampi(v2, 0, 255),
-                         (uint32_t)clampi(v3, 0, 255));
+        // max(min(v, 255), 0) is one instruction each (VIMNMX.RELU)
+        return pack_rgba((uint32_t)__vimin_s32_relu(v0, 255), (uint32_t)__vimin_s32_relu(v1, 255),
+                         (uint32_t)__vimin_s32_relu(v2, 255), (uint32_t)__vimin_s32_relu(v3, 255));
     } else {
         uint32_t se = 0, so = 0;
 #pragma unroll
