@@ -26,8 +26,17 @@ namespace normk {
 
 constexpr int kC2Group = 128, kC2Threads = 3 * kC2Group;
 // register budgets per group (setmaxnreg); they must add up to 3 x the launch allocation (80)
+#ifndef NORM_C2_ROLE_PERM
+#define NORM_C2_ROLE_PERM 1   // measured: +2.4 % at r = 21 with group A on the highest warp ids
+#endif
+#ifndef NORM_C2_SQRT_NOSEL
+#define NORM_C2_SQRT_NOSEL 1
+#endif
+#ifndef NORM_C2_CPAIR
+#define NORM_C2_CPAIR 0   // experimental group C: two pixels per thread (fewer instructions, measured slower: see DESIGN.md)
+#endif
 #ifndef NORM_C2_T
-#define NORM_C2_T 12
+#define NORM_C2_T 10
 #endif
 #ifndef NORM_C2_REGS_H4
 #define NORM_C2_REGS_H4 64  // RGBA blur: group A (H pass of four channels); groups B and C share the rest
@@ -53,7 +62,11 @@ struct Fused2Cfg {
     static constexpr int SW = 120;                      // output columns per strip
     static constexpr int BW = SW + 2 * HALO;            // blurred / intensity columns
     static constexpr int T = (MODE == 1 && !GRAY && R > 9) ? NORM_C2_T4 : NORM_C2_T;  // H-pass outputs per thread (4-channel H pass: fewer, for registers)
-    static constexpr int SEGS = (BW + T - 1) / T;       // 11
+    // H-pass items per row: SEGS full items of T columns + one short item of TAIL columns.  T = 10 with the 21-row batch
+    // gives 252 items for the group's 128 threads (two rounds, 98 % of the lanes busy) and no column is computed in vain.
+    static constexpr int SEGS = (T % 4 == 0) ? (BW + T - 1) / T : BW / T;
+    static constexpr int TAIL = (T % 4 == 0) ? 0 : BW - SEGS * T;
+    static_assert(TAIL % 2 == 0 && TAIL >= 0 && TAIL <= 4, "short H item: an even number of columns");
     static constexpr int HS = (BW + 3) / 4 * 4;         // 124: H plane row stride = columns actually stored
     static constexpr int HL = ((M + HALO) + 3) / 4 * 4; // staged left halo, 16-byte chunks
     static constexpr int OFF0 = HL - HALO - M;          // staged column of blurred column 0's first tap
@@ -62,7 +75,7 @@ struct Fused2Cfg {
     // rows per batch: a multiple of R, about 16.  The RGBA blur (four H planes) takes R itself from R = 13 on:
     // two times 13 or 15 rows would push its shared memory past half an SM and cost the second resident CTA
     // (measured: +11 % / +19 % at r = 13 / 15; the chain variants are faster with the longer batch).
-    static constexpr int RB = (R >= 13 && MODE == 1 && !GRAY) ? R : R * ((16 + R - 1) / R);
+    static constexpr int RB = (R >= 13 && MODE == 1 && !GRAY) ? R : (R == 3 ? 21 : R * ((16 + R - 1) / R));
     static constexpr int CH = MODE == 0 ? (GRAY ? 1 : 3) : (GRAY ? 2 : 4);
     // MODE 1 after grayscale (channels y, alpha): groups A and C both run the H pass (one channel each, staging
     // shared) and group B runs the V pass of both and stores RGBA8.  MODE 1 on RGBA: group A runs the H pass
@@ -80,10 +93,14 @@ struct Fused2Cfg {
     static constexpr int IS = 128;                      // intensity row stride
     static constexpr size_t kStgBytes = (size_t)RB * STG_STRIDE * 4;
     static constexpr size_t kHbBytes = (size_t)CH * RB * HS * 4;
-    static constexpr size_t kIstBytes = MODE == 0 ? (size_t)RB * IS * 4 : 0;  // intensity rows exist only when Sobel follows
+    // intensity rows exist only when Sobel follows.  Pair version of group C: two extra rows in front of every slot
+    // hold the previous batch's last two rows (group B re-stores them), so a slot is self-contained for the 3x3 window.
+    static constexpr int ICARRY = NORM_C2_CPAIR ? 2 : 0;
+    static constexpr size_t kIstBytes = MODE == 0 ? (size_t)(RB + ICARRY) * IS * 4 : 0;
+    static constexpr size_t kLutDBytes = (NORM_C2_CPAIR && MODE == 0) ? 256 * 8 : 0;  // luma of (c,c,c) as f64
     // + 64 words of slack: the last H segment's unused outputs read a few words past a staged row
-    static constexpr size_t kSmem = 2 * kStgBytes + 256 + 2 * kHbBytes + 2 * kIstBytes + 256 * 4 * 2 + 256;
-    static_assert(T % 4 == 0 && HS % 4 == 0, "16-byte H stores");
+    static constexpr size_t kSmem = 2 * kStgBytes + 256 + 2 * kHbBytes + 2 * kIstBytes + 256 * 4 * 2 + 256 + kLutDBytes;
+    static_assert(T % 2 == 0 && HS % 4 == 0, "8- or 16-byte H stores");
 };
 
 enum {
@@ -199,10 +216,15 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
     float *lumaLut = reinterpret_cast<float *>(smem_raw + 2 * C::kStgBytes + 256 + 2 * C::kHbBytes + 2 * C::kIstBytes);
     float *intLut = lumaLut + 256;
     uint8_t *flut = reinterpret_cast<uint8_t *>(intLut + 256);
+    double *lumaLutD = reinterpret_cast<double *>(flut + 256);
     constexpr int kHbFloats = C::CH * C::RB * C::HS;
-    constexpr int kIstFloats = C::RB * C::IS;
+    constexpr int kIstFloats = (C::RB + C::ICARRY) * C::IS;
 
-    const int tid = threadIdx.x;
+    // role index: which of the three groups a warp belongs to.  The warp scheduler prefers higher warp ids, so the
+    // mapping of roles to physical warps decides which group wins an issue slot when several are ready.
+    const int tid = NORM_C2_ROLE_PERM == 1   ? (int)((threadIdx.x + 128u) % 384u)                                        /* A = warps 8-11, C = 4-7, B = 0-3 */
+                    : NORM_C2_ROLE_PERM == 2 ? (int)(threadIdx.x >= 256u ? threadIdx.x - 256u : (threadIdx.x >= 128u ? threadIdx.x : threadIdx.x + 256u))  /* A = 8-11, B = 4-7, C = 0-3 */
+                                             : (int)threadIdx.x;
     const int W = (int)p.in.w, Himg = (int)p.in.h;
 
     if (tid < 256) {
@@ -210,6 +232,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         lumaLut[tid] = __fadd_rn(__fadd_rn(__fmul_rn(c, kLumaR), __fmul_rn(c, kLumaG)), __fmul_rn(c, kLumaB));
         intLut[tid] = __fsqrt_rn(__fmaf_rn(c, c, __fmaf_rn(c, c, __fmul_rn(c, c))));
         flut[tid] = p.lut.v[tid];
+        if (C::kLutDBytes) lumaLutD[tid] = (double)lumaLut[tid];
     }
     __syncthreads();
 
@@ -321,42 +344,79 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
 
                 const int slot = (int)(g & 1u);
                 bar_sync(kB2Empty0 + slot, kABParties);  // the consuming group(s) released this H-plane slot
-                // one thread = (row, segment) of the channels [c0, c0 + NCHH)
-                {
-                    for (int it = hid & (kC2Group - 1); it < C::RB * C::SEGS; it += kC2Group) {
-                        const int seg = it % C::SEGS, j = it / C::SEGS;
-                        const uint32_t *sp = stg + j * C::STG_STRIDE + C::OFF0 + seg * C::T;
-                        constexpr int TP = C::T / 2;
-                        float2 acc2[TP][NCHH];
+                // one thread = (row, TT consecutive blurred columns) of the channels [c0, c0 + NCHH): the TT + R - 1 source
+                // pixels are read once and scattered into TT x NCHH register accumulators, outputs paired so that every
+                // tap is one FFMA2.  The first tap pair {t[0], 0} initialises both halves by a multiply.
+                auto h_item = [&](auto tt_tag, int j, int col0) {
+                    constexpr int TT = decltype(tt_tag)::value, TP = TT / 2;
+                    const uint32_t *sp = stg + j * C::STG_STRIDE + C::OFF0 + col0;
+                    float2 acc2[TP][NCHH];
 #pragma unroll
-                        for (int i = 0; i < TP; ++i)
+                    for (int jj = 0; jj < TT + R - 1; ++jj) {
+                        const uint32_t px = sp[jj];
+                        float cv[NCHH];
 #pragma unroll
-                            for (int c = 0; c < NCHH; ++c) acc2[i][c] = make_float2(0.0f, 0.0f);
+                        for (int c = 0; c < NCHH; ++c) cv[c] = byte_f(px, C::chan_byte(c0 + c));
 #pragma unroll
-                        for (int jj = 0; jj < C::T + R - 1; ++jj) {
-                            const uint32_t px = sp[jj];
-                            float cv[NCHH];
+                        for (int i = 0; i < TP; ++i) {
+                            const int k = jj - 2 * i;  // tap of output 2i; output 2i+1 takes k-1 (a zero tap adds exactly 0)
+                            if (k == 0) {              // t[0]*v rounds like fma(t[0], v, 0); 0*v = +0 (v >= 0, finite)
 #pragma unroll
-                            for (int c = 0; c < NCHH; ++c) cv[c] = byte_f(px, C::chan_byte(c0 + c));
+                                for (int c = 0; c < NCHH; ++c) acc2[i][c] = __fmul2_rn(p.tp[0], make_float2(cv[c], cv[c]));
+                            } else if (k > 0 && k <= R) {
 #pragma unroll
-                            for (int i = 0; i < TP; ++i) {
-                                const int k = jj - 2 * i;  // tap of output 2i; output 2i+1 takes k-1 (a zero tap adds exactly 0)
-                                if (k >= 0 && k <= R) {
-#pragma unroll
-                                    for (int c = 0; c < NCHH; ++c)
-                                        acc2[i][c] = __ffma2_rn(p.tp[k], make_float2(cv[c], cv[c]), acc2[i][c]);
-                                }
+                                for (int c = 0; c < NCHH; ++c)
+                                    acc2[i][c] = __ffma2_rn(p.tp[k], make_float2(cv[c], cv[c]), acc2[i][c]);
                             }
                         }
-                        float *hp = Hb_base + slot * kHbFloats + j * C::HS + seg * C::T;
+                    }
+                    float *hp = Hb_base + slot * kHbFloats + j * C::HS + col0;
 #pragma unroll
-                        for (int c = 0; c < NCHH; ++c)
+                    for (int c = 0; c < NCHH; ++c) {
+                        if constexpr (TT % 4 == 0) {
 #pragma unroll
                             for (int i = 0; i < TP; i += 2)
-                                if (seg * C::T + 2 * i < C::HS)  // columns beyond the stored width are dropped
-                                    *reinterpret_cast<float4 *>(hp + (c0 + c) * (C::RB * C::HS) + 2 * i) =
-                                            make_float4(acc2[i][c].x, acc2[i][c].y, acc2[i + 1][c].x, acc2[i + 1][c].y);
+                                *reinterpret_cast<float4 *>(hp + (c0 + c) * (C::RB * C::HS) + 2 * i) =
+                                        make_float4(acc2[i][c].x, acc2[i][c].y, acc2[i + 1][c].x, acc2[i + 1][c].y);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < TP; ++i)
+                                *reinterpret_cast<float2 *>(hp + (c0 + c) * (C::RB * C::HS) + 2 * i) = acc2[i][c];
+                        }
                     }
+                };
+                for (int it = hid & (kC2Group - 1); it < C::RB * C::SEGS; it += kC2Group)
+                    h_item(std::integral_constant<int, C::T>{}, it / C::SEGS, (it % C::SEGS) * C::T);
+                if constexpr (C::TAIL > 0) {
+                    // the columns left over (the Sobel halo makes BW = 122): one short item per row, on one warp of the
+                    // group, a different one from batch to batch so that the four sub-partitions share them
+                    const int hl = hid & (kC2Group - 1);
+                    // scalar FMAs with the taps as constant-bank operands: the tap PAIRS stay the only uniform-register
+                    // resident set (a second use of them here makes the compiler copy them into vector registers)
+                    if ((hl >> 5) == (b & 3))
+                        for (int j = hl & 31; j < C::RB; j += 32) {
+                            const uint32_t *sp = stg + j * C::STG_STRIDE + C::OFF0 + C::SEGS * C::T;
+                            float acc[C::TAIL][NCHH];
+#pragma unroll
+                            for (int jj = 0; jj < C::TAIL + R - 1; ++jj) {
+                                const uint32_t px = sp[jj];
+#pragma unroll
+                                for (int c = 0; c < NCHH; ++c) {
+                                    const float v = byte_f(px, C::chan_byte(c0 + c));
+#pragma unroll
+                                    for (int o = 0; o < C::TAIL; ++o) {
+                                        const int k = jj - o;
+                                        if (k == 0) acc[o][c] = __fmul_rn(p.taps.t[0], v);
+                                        else if (k > 0 && k < R) acc[o][c] = __fmaf_rn(p.taps.t[k], v, acc[o][c]);
+                                    }
+                                }
+                            }
+                            float *hp = Hb_base + slot * kHbFloats + j * C::HS + C::SEGS * C::T;
+#pragma unroll
+                            for (int c = 0; c < NCHH; ++c)
+#pragma unroll
+                                for (int o = 0; o < C::TAIL; ++o) hp[(c0 + c) * (C::RB * C::HS) + o] = acc[o][c];
+                        }
                 }
                 __threadfence_block();
                 bar_arrive(kB2Full0 + slot, kABParties);
@@ -385,6 +445,9 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
             C2_ITEM_GEOMETRY();
             float2 vacc2[C::CH][R / 2];  // running outputs: slots (2i, 2i+1) packed, slot R-1 alone
             float vaccl[C::CH];
+#if NORM_C2_CPAIR
+            float icarry0 = 0.0f, icarry1 = 0.0f;
+#endif
 #pragma unroll
             for (int c = 0; c < C::CH; ++c) {
                 vaccl[c] = 0.0f;
@@ -397,7 +460,14 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                 bar_sync(kB2IEmpty0 + slot, 2 * kC2Group);  // group C has released this intensity slot
                 if (active) {
                     const float *hp = Hb_base + slot * kHbFloats + bcol;
+#if NORM_C2_CPAIR
+                    // blurred column bcol lives at index bcol + 1 (keeps group C's pixel pairs 8-byte aligned);
+                    // rows -2, -1 of the slot = the previous batch's last two rows
+                    float *ist = Ist_base + slot * kIstFloats + C::ICARRY * C::IS + bcol + 1;
+                    ist[-2 * C::IS] = icarry0, ist[-1 * C::IS] = icarry1;
+#else
                     float *ist = Ist_base + slot * kIstFloats + bcol;
+#endif
 #pragma unroll
                     for (int j = 0; j < C::RB; ++j) {
                         float v[C::CH];
@@ -424,16 +494,27 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                             } else {
                                 o = vacc2[c][done / 2].x, vacc2[c][done / 2].x = 0.0f;
                             }
-                            v[c] = round_rne(o);
+                            // round-half-even through the 1.5*2^23 trick; after grayscale only the byte (the low
+                            // mantissa bits of the biased sum) is needed, so the subtraction is skipped
+                            v[c] = GRAY ? __fadd_rn(o, 12582912.0f) : round_rne(o);
                         }
                         {
                             float I;
                             if (GRAY)
-                                I = intLut[__float_as_uint(__fadd_rn(v[0], 12582912.0f)) & 0xffu];
+                                I = intLut[__float_as_uint(v[0]) & 0xffu];
                             else
+#if NORM_C2_SQRT_NOSEL
+                                I = sqrt_rn_inrange0(__fmaf_rn(v[C::CH - 1], v[C::CH - 1],
+                                                              __fmaf_rn(v[C::CH > 1 ? 1 : 0], v[C::CH > 1 ? 1 : 0], __fmul_rn(v[0], v[0]))));
+#else
                                 I = sqrt_rn_inrange(__fmaf_rn(v[C::CH - 1], v[C::CH - 1],
                                                               __fmaf_rn(v[C::CH > 1 ? 1 : 0], v[C::CH > 1 ? 1 : 0], __fmul_rn(v[0], v[0]))));
+#endif
                             ist[j * C::IS] = I;
+#if NORM_C2_CPAIR
+                            if (j == C::RB - 2) icarry0 = I;
+                            if (j == C::RB - 1) icarry1 = I;
+#endif
                         }
                     }
                 }
@@ -450,6 +531,178 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
             return;
         }
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(NORM_C2_REGS_C));
+#if NORM_C2_CPAIR
+        // Pair version.  A thread owns TWO adjacent output columns (one 8-byte store, one 8-byte source load per row);
+        // warps 0/1 of the group take the column halves of batch rows [0, JH), warps 2/3 those of rows [JH, RB), so all
+        // four SM sub-partitions carry the same load.  Per-row overhead (pointer steps, loop control) is paid once per two
+        // pixels, and batches that lie wholly inside the band run a fully unrolled body with immediate shared-memory
+        // offsets; the first two and the last batch of a strip go through a generic per-row path.
+        const int tc = tid - 2 * kC2Group;
+        const int lane = tc & 31, warp = tc >> 5;
+        const int cp = (warp & 1) * 32 + lane;           // column pair of the strip: columns 2cp, 2cp + 1
+        const bool act = cp < C::SW / 2;
+        const int cpa = act ? cp : C::SW / 2 - 1;        // idle lanes shadow the last pair: valid addresses, results dropped
+        constexpr int JH = 3 * ((C::RB + 5) / 6);          // the longer share of a batch's rows, a multiple of three
+        // shared-memory address of lumaLutD minus 8 * (bits of 1.5*2^23), modulo 2^32: lutd + 8*bits = &lumaLutD[byte]
+        uint32_t lutd = (uint32_t)__cvta_generic_to_shared(lumaLutD) - (kMagicBits << 3);
+        asm volatile("" : "+r"(lutd));
+
+        bar_arrive(kB2IEmpty0, 2 * kC2Group);  // both intensity slots start out empty
+        bar_arrive(kB2IEmpty1, 2 * kC2Group);
+
+        for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
+            C2_ITEM_GEOMETRY();
+            const int x = x0 + 2 * cpa;                   // first column of the pair
+            const bool full_strip = x0 + C::SW <= W;      // every pair of the strip lies inside the image
+            // intensity columns (index = blurred column + 1): the pair at ic, ic + 1; ClampToEdge on the blurred image
+            const int ic = 2 * cpa + 2;
+            const int il = (x - 1 < 0) ? ic : ic - 1;
+            const int ir = (x + 2 > W - 1) ? ic + 1 : ic + 2;
+            const int xs = min(x, W - 1);                 // ragged strips: keep the source / output addresses inside the row
+            const uint8_t *in_col = p.in.ptr + (size_t)f * p.in.frame_stride + (size_t)xs * 4;
+            uint8_t *out_col = p.out.ptr + (size_t)f * p.out.frame_stride + (size_t)xs * 4;
+            double m5[5] = {0, 0, 0, 0, 0};
+
+            // SSIM moments of one pixel: x = luma of the (c,c,c) result (f64 table), y = f32 luma of the source pixel
+            auto ssim_px = [&](uint32_t cb, uint32_t spx) {
+                double xv;
+                asm("ld.shared.f64 %0, [%1];" : "=d"(xv) : "r"(lutd + (cb << 3)));
+                const double yv = (double)luma_ssim(spx);
+                m5[0] += xv;
+                m5[1] += yv;
+                m5[2] = fma(xv, xv, m5[2]);
+                m5[3] = fma(yv, yv, m5[3]);
+                m5[4] = fma(xv, yv, m5[4]);
+            };
+
+            for (int b = 0; b < nbatch; ++b, ++g) {
+                const int slot = (int)(g & 1u);
+                bar_sync(kB2IFull0 + slot, 2 * kC2Group);
+                const float *ist = Ist_base + slot * kIstFloats + C::ICARRY * C::IS;  // batch row j at ist + j*IS
+                const int n0 = b * C::RB - (R - 1);   // blurred row (relative to o_lo) that batch row 0 completes
+                const int yfirst = o_lo + n0 - 1;     // output row emitted when batch row 0 arrives
+                // this warp's rows [JA, JB) of the batch; the two warp pairs swap the longer share from batch to batch
+                const bool first_half = ((warp >> 1) ^ (b & 1)) == 0;
+                const int JA = first_half ? 0 : JH, JB = first_half ? JH : C::RB;
+                // Rows [FA, FB) of the share run the fast body: their three window rows exist (n >= 2), nothing clamps,
+                // the row is not the band's last (n < NB - 1) and the source rows fetched ahead (three below) exist;
+                // every row of the batch lies in the SSIM row range.  The rows before and after go through the generic code.
+                const bool fast_ok = full_strip && (!p.do_ssim || (yfirst >= (int)p.ssim_y0 && yfirst + C::RB <= (int)p.ssim_y1));
+                const int FA = fast_ok ? min(max(JA, 2 - n0), JB) : JB, FB = fast_ok ? max(min(JB, NB - 4 - n0), FA) : JB;
+                const bool fast = FA < FB;
+                if (fast) {
+                    // ---- interior batch: three rows per trip (the 3x3 window rotates statically), window rows JA-2, JA-1
+                    // primed from shared memory, shared-memory offsets immediate, source pixels three rows ahead
+                    auto body = [&](auto ssim_tag) {
+                        constexpr bool SSIM = decltype(ssim_tag)::value;
+                        const float *pl = ist + FA * C::IS + il, *pc = ist + FA * C::IS + ic, *pr = ist + FA * C::IS + ir;
+                        float wl[3], wa[3], wb[3], wr[3];  // window rows: (left, pair, right)
+#pragma unroll
+                        for (int q = 0; q < 2; ++q) {
+                            const float2 cc = *reinterpret_cast<const float2 *>(pc + (q - 2) * C::IS);
+                            wl[q + 1] = pl[(q - 2) * C::IS], wa[q + 1] = cc.x, wb[q + 1] = cc.y, wr[q + 1] = pr[(q - 2) * C::IS];
+                        }
+                        const int y = yfirst + FA;
+                        const uint8_t *ip = in_col + (size_t)y * p.in.pitch;
+                        uint8_t *op = out_col + (size_t)y * p.out.pitch;
+                        uint2 sp[3];
+                        if (SSIM) {
+#pragma unroll
+                            for (int q = 0; q < 3; ++q) {
+                                sp[q] = *reinterpret_cast<const uint2 *>(ip);
+                                ip += p.in.pitch;
+                            }
+                        }
+                        int j = FA;
+                        for (; j + 3 <= FB; j += 3) {
+#pragma unroll
+                            for (int jj = 0; jj < 3; ++jj) {
+                                // rows: new = slot jj, previous = slot (jj+2)%3, the one before = slot (jj+1)%3
+                                constexpr int dummy = 0;
+                                (void)dummy;
+                                const int t = jj, m = (jj + 2) % 3, bt = (jj + 1) % 3;
+                                const float2 cc = *reinterpret_cast<const float2 *>(pc + jj * C::IS);
+                                wl[t] = pl[jj * C::IS], wa[t] = cc.x, wb[t] = cc.y, wr[t] = pr[jj * C::IS];
+                                const uint32_t cb0 = sobel_mag_bits(wl[t], wa[t], wb[t], wl[m], wb[m], wl[bt], wa[bt], wb[bt]);
+                                const uint32_t cb1 = sobel_mag_bits(wa[t], wb[t], wr[t], wa[m], wr[m], wa[bt], wb[bt], wr[bt]);
+                                if (act) *reinterpret_cast<uint2 *>(op) = make_uint2(__byte_perm(cb0, 0xffu, 0x4000), __byte_perm(cb1, 0xffu, 0x4000));
+                                op += p.out.pitch;
+                                if (SSIM) {
+                                    const uint2 s2 = sp[jj];
+                                    sp[jj] = *reinterpret_cast<const uint2 *>(ip);
+                                    ip += p.in.pitch;
+                                    ssim_px(cb0, s2.x);
+                                    ssim_px(cb1, s2.y);
+                                }
+                            }
+                            pl += 3 * C::IS, pc += 3 * C::IS, pr += 3 * C::IS;
+                        }
+                        // rows left over when the share is not a multiple of three: all three window rows from shared memory
+                        for (; j < FB; ++j) {
+                            const float *rt = ist + j * C::IS, *rm = rt - C::IS, *rb = rm - C::IS;
+                            const int yy = yfirst + j;
+                            const float2 ct = *reinterpret_cast<const float2 *>(rt + ic), cm = *reinterpret_cast<const float2 *>(rm + ic),
+                                         cbm = *reinterpret_cast<const float2 *>(rb + ic);
+                            const uint32_t cb0 = sobel_mag_bits(rt[il], ct.x, ct.y, rm[il], cm.y, rb[il], cbm.x, cbm.y);
+                            const uint32_t cb1 = sobel_mag_bits(ct.x, ct.y, rt[ir], cm.x, rm[ir], cbm.x, cbm.y, rb[ir]);
+                            if (act) *reinterpret_cast<uint2 *>(out_col + (size_t)yy * p.out.pitch) =
+                                    make_uint2(__byte_perm(cb0, 0xffu, 0x4000), __byte_perm(cb1, 0xffu, 0x4000));
+                            if (SSIM) {
+                                const uint2 s2 = *reinterpret_cast<const uint2 *>(in_col + (size_t)yy * p.in.pitch);
+                                ssim_px(cb0, s2.x);
+                                ssim_px(cb1, s2.y);
+                            }
+                        }
+                    };
+                    if (p.do_ssim) body(std::true_type{});
+                    else body(std::false_type{});
+                }
+                if (FA > JA || FB < JB) {
+                    // ---- generic path: every row checks for itself what it completes (band / image edges, SSIM range)
+                    for (int j = JA; j < JB; ++j) {
+                        if (j == FA) j = FB;  // (FA == FB == JB when nothing ran fast)
+                        if (j >= JB) break;
+                        const int n = n0 + j;
+                        if (n < 0 || n >= NB) continue;
+                        const float *rt = ist + j * C::IS, *rm = rt - C::IS, *rb = (o_lo + n - 2 < 0) ? rm : rm - C::IS;
+                        // one or two emissions: row y = o_lo + n - 1, and at the bottom of the image also row y + 1,
+                        // whose "row below" clamps to itself
+                        for (int e = 0; e < 2; ++e) {
+                            const int y = o_lo + n - 1 + e;
+                            if (e == 1) {
+                                if (!(yb == Himg && n == NB - 1)) break;
+                                rb = (o_lo + n - 1 < 0) ? rt : rm, rm = rt;  // a one-row image: the row above clamps too
+                            }
+                            if (y < ya || (e == 0 && n == 0)) continue;
+                            const bool ss_row = p.do_ssim && (uint32_t)(y - (int)p.ssim_y0) < p.ssim_y1 - p.ssim_y0;
+#pragma unroll
+                            for (int h = 0; h < 2; ++h) {
+                                const int xx = x + h;
+                                if (!act || xx >= W) continue;
+                                const int c0 = ic + h;
+                                const int cl = (xx - 1 < 0) ? c0 : c0 - 1, cr = (xx + 1 > W - 1) ? c0 : c0 + 1;
+                                const uint32_t cb = sobel_mag_bits(rt[cl], rt[c0], rt[cr], rm[cl], rm[cr], rb[cl], rb[c0], rb[cr]);
+                                *reinterpret_cast<uint32_t *>(out_col + (size_t)y * p.out.pitch + 4 * h) = __byte_perm(cb, 0xffu, 0x4000);
+                                if (ss_row) ssim_px(cb, *reinterpret_cast<const uint32_t *>(in_col + (size_t)y * p.in.pitch + 4 * h));
+                            }
+                        }
+                    }
+                }
+                __threadfence_block();
+                bar_arrive(kB2IEmpty0 + slot, 2 * kC2Group);
+            }
+            if (p.do_ssim) {
+#pragma unroll
+                for (int k = 0; k < 5; ++k) {
+                    const double sm = warp_sum(act ? m5[k] : 0.0);
+                    if (lane == 0) red[k][warp] = sm;
+                }
+                bar_sync(kB2C, kC2Group);
+                if (tc < 5) p.partials[item * 5 + tc] = ((red[tc][0] + red[tc][1]) + red[tc][2]) + red[tc][3];
+                bar_sync(kB2C, kC2Group);
+            }
+        }
+#else
         const int tc = tid - 2 * kC2Group;  // output column of the strip
         const int lane = tc & 31, warp = tc >> 5;
         // shared-memory address of lumaLut minus 4 * (bits of 1.5*2^23), modulo 2^32: lut_biased + 4*bits = &lumaLut[byte]
@@ -585,6 +838,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                 bar_sync(kB2C, kC2Group);
             }
         }
+#endif  // NORM_C2_CPAIR
     }
 #undef C2_ITEM_GEOMETRY
 }
