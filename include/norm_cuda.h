@@ -281,9 +281,71 @@ norm_status norm_cuda_ipc_open(norm_ctx *ctx, const uint8_t handle[64], void **d
 norm_status norm_cuda_ipc_close(norm_ctx *ctx, void *device_ptr);
 /* Halo exchange: copies `nrows` rows starting at src_row of a (local or peer-mapped) RGBA8
  * buffer with pitch src_pitch into rows [dst_row, dst_row+nrows) of frame 0 of `dst`, on the
- * context's stream (asynchronous; order with norm_cuda_sync). */
+ * context's stream (asynchronous; order with norm_cuda_sync).  The copy is ordered with THIS
+ * context's stream only: nothing orders it with the peer process that produces the source rows.
+ * Callers whose source changes use the norm_cuda_band_* calls below, which carry that ordering
+ * (interprocess events); with this call alone the source must be complete before it is queued. */
 norm_status norm_cuda_copy_rows(norm_ctx *ctx, norm_img *dst, uint32_t dst_row, const void *src_device_ptr,
                                 size_t src_pitch, uint32_t src_row, uint32_t nrows);
+
+/* ---- the row-band scheduler behind one handle ----------------------------------------------
+ * No reference counterpart (the reference is single-device); the contract is
+ * BASELINE.json configs[4].  One norm_band per rank (one process per GPU, or several ranks in
+ * one process).  A rank owns rows [row0, row0 + rows) of the width x height image; `src` / `dst`
+ * (norm_cuda_band_src / _dst) are its extended band images: halo_up + rows + halo_down rows, the
+ * owned rows starting at row halo_up.  Life cycle:
+ *
+ *   norm_cuda_band_create            plan (norm_plan_band), allocate src/dst, streams, events
+ *   norm_cuda_band_export            256-byte handle: CUDA IPC handles of src and of two events
+ *   [exchange the handles of all ranks through any host side channel]
+ *   norm_cuda_band_connect           open the neighbours' memory and events (peer access on)
+ *   [write the owned rows of src: norm_cuda_copy_rows / norm_cuda_upload / a kernel on the
+ *    context's stream], then norm_cuda_band_publish
+ *   [host barrier over the ranks: every rank has published]
+ *   norm_cuda_band_step_async        one pass of the chain over the band, see below
+ *
+ * norm_cuda_band_step_async queues, without ever blocking the host:
+ *   - on the band's halo stream: wait for the neighbours' published rows, copy the halo rows over
+ *     NVLink (cudaMemcpy2DAsync, one copy per neighbour and side), record "halo rows are in";
+ *   - on the context's stream: the chain on the INTERIOR output rows (their stencil touches no
+ *     halo row) at once, then - after "halo rows are in" - the two edge strips;
+ *   - the SSIM moments (5 doubles) of the owned rows into moments_dev (device memory, may be
+ *     NULL), summed in the fixed order interior, top strip, bottom strip;
+ *   - on the band's side stream (norm_cuda_band_side_stream): a wait for those moments, so that a
+ *     norm_nccl_allreduce_sum_f64 queued there runs beside the next step instead of inside it.
+ *     The caller alternates between two moments buffers when it queues steps back to back.
+ * Settings no fused kernel covers run the whole extended band after the halo rows are in.
+ *
+ * When the owned rows CHANGE from step to step: norm_cuda_band_begin_update (the context's
+ * stream waits until every neighbour has finished copying out of this band), write the rows,
+ * norm_cuda_band_publish, host barrier, norm_cuda_band_step_async, host barrier.  The two host
+ * barriers order the ENQUEUE of the event records and waits between processes (a CUDA event
+ * carries no step count); they do not wait for the GPU. */
+typedef struct norm_band norm_band;
+typedef struct NormBandHandle {
+    uint8_t mem[64];          /* cudaIpcMemHandle_t of the band's src image */
+    uint8_t ready_event[64];  /* cudaIpcEventHandle_t: owned rows written (norm_cuda_band_publish) */
+    uint8_t halo_event[64];   /* cudaIpcEventHandle_t: this rank's halo copies are done */
+    uint64_t pitch;           /* bytes per row of src */
+    uint64_t local_ptr, local_ready, local_halo, pid; /* the same three objects for ranks inside one process */
+    uint32_t row0, rows, halo_up, halo_down;
+    int32_t rank, device;
+} NormBandHandle;
+norm_status norm_cuda_band_create(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t width, uint32_t height,
+                                  int32_t nranks, int32_t rank, norm_band **out);
+norm_status norm_cuda_band_destroy(norm_band *band);
+norm_status norm_cuda_band_layout(const norm_band *band, uint32_t *row0, uint32_t *rows, uint32_t *halo_up,
+                                  uint32_t *halo_down);
+norm_img *norm_cuda_band_src(norm_band *band);
+norm_img *norm_cuda_band_dst(norm_band *band);
+norm_status norm_cuda_band_export(norm_band *band, NormBandHandle *handle);
+norm_status norm_cuda_band_connect(norm_band *band, const NormBandHandle *all_ranks, int32_t nranks);
+norm_status norm_cuda_band_begin_update(norm_band *band);
+norm_status norm_cuda_band_publish(norm_band *band);
+norm_status norm_cuda_band_step_async(norm_band *band, uint32_t flags, double *moments_dev);
+norm_status norm_cuda_band_side_stream(norm_band *band, void **cuda_stream);
+/* Waits for everything the band has queued (halo, context and side streams). */
+norm_status norm_cuda_band_sync(norm_band *band);
 
 /* Single stages, for callers that compose their own pipeline (EffectPipelineBuilder::
  * add_effect, effect_pipeline.rs:92-123) and for per-stage parity tests. */

@@ -65,6 +65,16 @@ class NormDrawUniform(C.Structure):
                 ("circle_radius", C.c_float), ("camera_view_proj", (C.c_float * 4) * 4)]
 
 
+class NormBandHandle(C.Structure):
+    """include/norm_cuda.h: what one rank of a row-band sharded image tells the others (256 bytes)."""
+    _fields_ = [("mem", C.c_uint8 * 64), ("ready_event", C.c_uint8 * 64), ("halo_event", C.c_uint8 * 64),
+                ("pitch", C.c_uint64), ("local_ptr", C.c_uint64), ("local_ready", C.c_uint64),
+                ("local_halo", C.c_uint64), ("pid", C.c_uint64),
+                ("row0", C.c_uint32), ("rows", C.c_uint32), ("halo_up", C.c_uint32), ("halo_down", C.c_uint32),
+                ("rank", C.c_int32), ("device", C.c_int32)]
+
+
+assert C.sizeof(NormBandHandle) == 256
 assert C.sizeof(NormShapeUniform) == 16 and C.sizeof(NormCircleData) == 16 and C.sizeof(NormDrawUniform) == 80
 NORM_MAX_CIRCLES = 256
 
@@ -114,6 +124,18 @@ PROTOTYPES = {
     "norm_cuda_ipc_open": (_i32, [_vp, _vp, C.POINTER(_vp)]),
     "norm_cuda_ipc_close": (_i32, [_vp, _vp]),
     "norm_cuda_copy_rows": (_i32, [_vp, _vp, _u32, _vp, _sz, _u32, _u32]),
+    "norm_cuda_band_create": (_i32, [_vp, _fu, _u32, _u32, _i32, _i32, C.POINTER(_vp)]),
+    "norm_cuda_band_destroy": (_i32, [_vp]),
+    "norm_cuda_band_layout": (_i32, [_vp, C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_u32)]),
+    "norm_cuda_band_src": (_vp, [_vp]),
+    "norm_cuda_band_dst": (_vp, [_vp]),
+    "norm_cuda_band_export": (_i32, [_vp, C.POINTER(NormBandHandle)]),
+    "norm_cuda_band_connect": (_i32, [_vp, C.POINTER(NormBandHandle), _i32]),
+    "norm_cuda_band_begin_update": (_i32, [_vp]),
+    "norm_cuda_band_publish": (_i32, [_vp]),
+    "norm_cuda_band_step_async": (_i32, [_vp, _u32, _vp]),
+    "norm_cuda_band_side_stream": (_i32, [_vp, C.POINTER(_vp)]),
+    "norm_cuda_band_sync": (_i32, [_vp]),
     "norm_cuda_front": (_i32, [_vp, _fu, _u32, _vp, _vp]),
     "norm_cuda_blur": (_i32, [_vp, _u32, _vp, _vp]),
     "norm_cuda_sobel": (_i32, [_vp, _vp, _vp]),

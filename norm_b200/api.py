@@ -429,6 +429,55 @@ class Context:
         return m
 
 
+class Band:
+    """One rank's share of a row-band sharded image (norm_cuda_band_*, include/norm_cuda.h): the halo exchange over
+    NVLink, the overlapped interior / edge launches and the SSIM moments behind one handle."""
+
+    def __init__(self, ctx, f, width, height, nranks, rank):
+        self.ctx, self.lib = ctx, ctx.lib
+        h = C.c_void_p()
+        ctx._ok(self.lib.norm_cuda_band_create(ctx.h, Context._raw(f), width, height, nranks, rank, C.byref(h)))
+        self.h, self.width, self.height, self.nranks, self.rank = h, width, height, nranks, rank
+        a, b, c, d = C.c_uint32(), C.c_uint32(), C.c_uint32(), C.c_uint32()
+        ctx._ok(self.lib.norm_cuda_band_layout(h, a, b, c, d))
+        self.row0, self.rows, self.halo_up, self.halo_down = a.value, b.value, c.value, d.value
+        self.src = DeviceImage(ctx, C.c_void_p(self.lib.norm_cuda_band_src(h)))
+        self.dst = DeviceImage(ctx, C.c_void_p(self.lib.norm_cuda_band_dst(h)))
+
+    def export(self):
+        hd = _lib.NormBandHandle()
+        self.ctx._ok(self.lib.norm_cuda_band_export(self.h, C.byref(hd)))
+        return bytes(hd)
+
+    def connect(self, handles):
+        """handles: the export() of every rank, ordered by rank."""
+        arr = (_lib.NormBandHandle * len(handles))(*[_lib.NormBandHandle.from_buffer_copy(x) for x in handles])
+        self.ctx._ok(self.lib.norm_cuda_band_connect(self.h, arr, len(handles)))
+
+    def begin_update(self): self.ctx._ok(self.lib.norm_cuda_band_begin_update(self.h))
+    def publish(self): self.ctx._ok(self.lib.norm_cuda_band_publish(self.h))
+
+    def step_async(self, flags=NORM_CS_REFERENCE, moments_dev=None):
+        self.ctx._ok(self.lib.norm_cuda_band_step_async(self.h, flags, C.c_void_p(moments_dev) if moments_dev else None))
+
+    def side_stream(self):
+        p = C.c_void_p()
+        self.ctx._ok(self.lib.norm_cuda_band_side_stream(self.h, C.byref(p)))
+        return p.value or 0
+
+    def sync(self): self.ctx._ok(self.lib.norm_cuda_band_sync(self.h))
+
+    def own_rows_of(self, img):
+        """The owned rows of an extended band image (src or dst) as a (rows, width, 4) array."""
+        return img.download()[0][self.halo_up:self.halo_up + self.rows]
+
+    def destroy(self):
+        if self.h:
+            self.lib.norm_cuda_band_destroy(self.h)
+            self.h = None
+            self.src.handle = self.dst.handle = None  # owned by the band
+
+
 class Texture:
     """texture.rs:22-80: `from_image` = rgba8() + upload; here both happen on the GPU."""
 

@@ -181,7 +181,7 @@ __device__ __forceinline__ void blur_only_consumer(const FusedParams &p, const f
         const uint32_t irem = (uint32_t)(item - (size_t)f * items_per_frame);
         const int band = (int)(irem / p.strips), strip = (int)(irem - (uint32_t)band * p.strips);
         const int x0 = strip * C::SW;
-        const int ya = band * (int)p.band_rows, yb = min(ya + (int)p.band_rows, Himg);
+        const int ya = (int)p.out_y0 + band * (int)p.band_rows, yb = min(ya + (int)p.band_rows, (int)p.out_y1);
         const int NB = yb - ya;  // MODE 1: blurred rows == output rows
         const int nbatch = (NB + R - 1 + C::RB - 1) / C::RB;
         const int bx = x0 + bcol;
@@ -248,7 +248,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
     const uint32_t irem = (uint32_t)(item - (size_t)f * items_per_frame);                               \
     const int band = (int)(irem / p.strips), strip = (int)(irem - (uint32_t)band * p.strips);           \
     const int x0 = strip * C::SW;                                                                       \
-    const int ya = band * (int)p.band_rows, yb = min(ya + (int)p.band_rows, Himg);                      \
+    const int ya = (int)p.out_y0 + band * (int)p.band_rows, yb = min(ya + (int)p.band_rows, (int)p.out_y1);                      \
     const int o_lo = max(ya - C::HALO, 0), o_hi = min(yb - 1 + C::HALO, Himg - 1); /* blurred rows needed */ \
     const int NB = o_hi - o_lo + 1;                                                                     \
     const int Q = NB + R - 1; /* rows of the clamped source sequence s(q) = clamp(o_lo - M + q) */      \

@@ -11,6 +11,7 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <unistd.h>
 #include <type_traits>
 #include <vector>
 
@@ -50,6 +51,10 @@ struct Slot {
     DevBuf tmp[2];
     DevBuf partials;
     DevBuf stage_in, stage_out;
+    // row window of the next fused launches (band mode): produce output rows [win_y0, win_y1) only (0, 0 = all rows)
+    // and add the window's SSIM moments to what d_moments already holds instead of overwriting it
+    uint32_t win_y0 = 0, win_y1 = 0;
+    bool accumulate = false;
 };
 
 thread_local std::string g_create_error;
@@ -454,16 +459,21 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
     for (int k = 0; k <= R; ++k)
         fp.tp[k] = make_float2(k < R ? fp.taps.t[k] : 0.0f, k >= 1 ? fp.taps.t[k - 1] : 0.0f);
     fp.strips = (in.w + C::SW - 1) / C::SW;
+    // output rows of this launch: all of them, or the slot's window (band mode)
+    fp.out_y0 = slot.win_y1 ? slot.win_y0 : 0u;
+    fp.out_y1 = slot.win_y1 ? std::min(slot.win_y1, in.h) : in.h;
+    if (fp.out_y0 >= fp.out_y1) return fail(ctx, NORM_E_INVALID_ARG, "empty output row window");
+    const uint32_t out_rows = fp.out_y1 - fp.out_y0;
     // enough work items to fill the machine ~4 times over; bands no shorter than 64 rows
     const size_t slots = (size_t)ctx->sm_count * per_sm;
     const size_t base_items = (size_t)fp.strips * in.frames;
     uint32_t bands = (uint32_t)std::min<size_t>(std::max<size_t>(1, (4 * slots + base_items - 1) / base_items),
-                                                std::max<uint32_t>(1, in.h / 64));
-    fp.band_rows = (in.h + bands - 1) / bands;
-    fp.bands = (in.h + fp.band_rows - 1) / fp.band_rows;
+                                                std::max<uint32_t>(1, out_rows / 64));
+    fp.band_rows = (out_rows + bands - 1) / bands;
+    fp.bands = (out_rows + fp.band_rows - 1) / fp.band_rows;
     fp.invert = p.inv ? 1u : 0u;
     fp.do_ssim = (d_ssim || d_moments) ? 1u : 0u;
-    fp.ssim_y0 = y0, fp.ssim_y1 = std::min(y1, in.h);
+    fp.ssim_y0 = std::max(y0, fp.out_y0), fp.ssim_y1 = std::max(fp.ssim_y0, std::min(y1, fp.out_y1));
     const uint32_t items_per_frame = fp.strips * fp.bands;
     if (fp.do_ssim) {
         NORM_TRY(ensure_buf(ctx, slot.partials, (size_t)in.frames * items_per_frame * 5 * sizeof(double)));
@@ -474,7 +484,8 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
     LAUNCH_CHECK(ctx);
     if (fp.do_ssim) {
         const double npix = (double)in.w * (double)(fp.ssim_y1 - fp.ssim_y0);
-        ssim_finalize_kernel<<<in.frames, 256, 0, slot.stream>>>(fp.partials, items_per_frame, npix, d_moments, d_ssim);
+        ssim_finalize_kernel<<<in.frames, 256, 0, slot.stream>>>(fp.partials, items_per_frame, npix, d_moments, d_ssim,
+                                                                 slot.accumulate ? 1 : 0);
         LAUNCH_CHECK(ctx);
     }
     return NORM_OK;
@@ -572,6 +583,21 @@ norm_status try_launch_chain_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p
 #undef X
     default: *fused = false; return NORM_OK;
     }
+}
+
+// Rows of SOURCE needed above / below an output row by the chained stencil stages (blur, sharpen, Sobel).
+norm_status stencil_reach(const NormFeatureUniform *f, uint32_t *up_out, uint32_t *down_out) {
+    uint32_t up = 0, down = 0;
+    if (f->blur == 1) {
+        Taps t;
+        if (make_taps(f->blur_radius, t) != NORM_OK) return NORM_E_INVALID_ARG;
+        up += (uint32_t)(-t.dmin);
+        down += (uint32_t)(t.dmin + t.n - 1);
+    }
+    if (f->sharpen == 1) up += 1, down += 1;
+    if (f->edge_detect == 1) up += 1, down += 1;
+    *up_out = up, *down_out = down;
+    return NORM_OK;
 }
 
 // Row sub-view of every frame: rows [y0, y1).
@@ -1625,19 +1651,13 @@ norm_status norm_plan_band(const NormFeatureUniform *f, uint32_t height, int32_t
                            uint32_t *rows, uint32_t *halo_up, uint32_t *halo_down) {
     if (!f || !row0 || !rows || !halo_up || !halo_down) return NORM_E_INVALID_ARG;
     NORM_TRY(norm_plan_frames(height, nranks, rank, row0, rows));
-    // rows of SOURCE needed above / below an output row by the chained stencil stages
     uint32_t up = 0, down = 0;
-    if (f->blur == 1) {
-        Taps t;
-        if (make_taps(f->blur_radius, t) != NORM_OK) return NORM_E_INVALID_ARG;
-        up += (uint32_t)(-t.dmin);
-        down += (uint32_t)(t.dmin + t.n - 1);
-    }
-    if (f->sharpen == 1) up += 1, down += 1;
-    if (f->edge_detect == 1) up += 1, down += 1;
+    NORM_TRY(stencil_reach(f, &up, &down));
     *halo_up = std::min(up, *row0);
     *halo_down = std::min(down, height - (*row0 + *rows));
     return NORM_OK;
 }
 
 }  // extern "C"
+
+#include "band.inc"

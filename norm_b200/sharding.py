@@ -5,7 +5,11 @@ bands: `band_source_rows` says which global rows a rank must hold (owned rows + 
 halo), `halo_requests` which of them come from which neighbour - the halo rows are the
 neighbours' OWNED rows next to the seam, fetched with peer copies over NVLink.
 """
-from .api import plan_band, plan_frames  # noqa: F401
+import ctypes as _C
+
+import numpy as _np
+
+from .api import Band, plan_band, plan_frames, ssim_from_moments  # noqa: F401
 
 
 def band_layout(f, height, nranks, rank):
@@ -36,3 +40,49 @@ def halo_requests(f, height, nranks, rank):
             else:
                 raise AssertionError("row without owner")
     return out
+
+
+class BandJob:
+    """One rank of a row-band sharded image (BASELINE configs[4]) ready to step: a Band (norm_cuda_band_*), the
+    neighbours connected through `allgather` (any callable that returns every rank's bytes object, ordered by rank:
+    torch.distributed.all_gather_object, mpi4py, a list for ranks inside one process), two device buffers for the
+    SSIM moments and, when `comm` (norm_b200.nccl.Comm) is given, the all-reduce of the moments on the band's side
+    stream.  The host blocks nowhere inside step()."""
+
+    def __init__(self, ctx, f, width, height, nranks, rank, allgather, comm=None):
+        self.ctx, self.comm, self.k = ctx, comm, 0
+        self.band = Band(ctx, f, width, height, nranks, rank)
+        self.band.connect(allgather(self.band.export()))
+        self.mom = [ctx.image_create(64, 1, 1) for _ in range(2)]  # 256 bytes of device memory each
+        self.side = self.band.side_stream()
+        self.halo_bytes = (self.band.halo_up + self.band.halo_down) * width * 4
+
+    def fill_rows(self, device_ptr, pitch, first_row, nrows):
+        """Copies rows [first_row, first_row + nrows) of the rank's OWNED rows from a device buffer into the band."""
+        self.ctx.copy_rows(self.band.src, self.band.halo_up + first_row, device_ptr, pitch, 0, nrows)
+
+    def publish(self):
+        self.band.publish()
+
+    def step(self, flags):
+        m = self.mom[self.k & 1]
+        self.band.step_async(flags, m.device_ptr)
+        if self.comm is not None:
+            self.comm.allreduce_device(m.device_ptr, 5, self.side)
+        self.k += 1
+        return m
+
+    def sync(self):
+        self.band.sync()
+
+    def moments(self):
+        """The last step's moments (summed over ranks when a communicator was given); waits for the band."""
+        self.sync()
+        m = self.mom[(self.k - 1) & 1]
+        return _np.frombuffer(m.download()[0].tobytes()[:40], _np.float64).copy()
+
+    def close(self):
+        self.sync()
+        for m in self.mom:
+            m.destroy()
+        self.band.destroy()

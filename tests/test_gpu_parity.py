@@ -452,6 +452,47 @@ def test_band_mode_emulated_ranks(ctx, oracle, nranks):
             x.destroy()
 
 
+@pytest.mark.parametrize("nranks", [1, 2, 3, 5])
+def test_band_scheduler_emulated_ranks(oracle, nranks):
+    """configs[4] through norm_cuda_band_*: one band object per emulated rank (one context each, all on this
+    GPU, handles exchanged inside the process), halo rows by peer copies on the halo stream, interior rows
+    launched before the halo rows arrive, edge strips after; owned rows and the summed SSIM moments must equal
+    the oracle on the whole image.  Two steps in a row with changed source rows exercise begin_update / publish."""
+    w = 300
+    for kw, h in ((dict(blur=1, blur_radius=21, edge_detect=1), 211), (dict(grayscale=1, blur=1, blur_radius=7, edge_detect=1), 97),
+                  (dict(blur=1, blur_radius=5, sharpen=1), 64), (dict(blur=1, blur_radius=21, edge_detect=1), 40)):
+        f = uniform(w, h, **kw)
+        ctxs = [nb.Context(0) for _ in range(nranks)]
+        bands = [nb.Band(c, f, w, h, nranks, r) for r, c in enumerate(ctxs)]
+        handles = [b.export() for b in bands]
+        for b in bands:
+            b.connect(handles)
+        moms = [c.image_create(64, 1, 1) for c in ctxs]  # 256 bytes of device memory each
+        for step, seed in enumerate((31, 32)):
+            img = smooth_rgba(w, h, seed=seed)
+            for b in bands:
+                b.begin_update()
+                ext = np.full((b.src.height, w, 4), 0xAB, np.uint8)  # halo rows poisoned: they must come from the peers
+                ext[b.halo_up:b.halo_up + b.rows] = img[b.row0:b.row0 + b.rows]
+                b.src.upload(ext)
+                b.publish()
+            for b, m in zip(bands, moms):  # (all ranks have published: the in-process stand-in for the host barrier)
+                b.step_async(nb.NORM_CS_RAW, m.device_ptr)
+            for b in bands:
+                b.sync()
+            got = np.concatenate([b.own_rows_of(b.dst) for b in bands])
+            total = sum(np.frombuffer(m.download()[0].tobytes()[:40], np.float64) for m in moms)
+            eo, es = oracle.chain(img, oracle_uniform(oracle, f), oracle.CS_RAW)
+            assert np.array_equal(got, eo), (nranks, kw, h, step)
+            assert abs(nb.ssim_from_moments(total, w * h) - es) <= SSIM_TIGHT, (nranks, kw, h, step)
+        for m in moms:
+            m.destroy()
+        for b in bands:
+            b.destroy()
+        for c in ctxs:
+            c.close()
+
+
 def test_effects_flips(ctx, oracle):
     """FlipX / FlipY (feature_uniform.rs:143-175): the finished frame is mirrored."""
     for (w, h) in [(5, 7), (130, 70), (333, 41)]:
