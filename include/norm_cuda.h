@@ -68,7 +68,13 @@ typedef struct NormFeatureUniform {
 enum {
     NORM_CS_REFERENCE = 0u, /* input is sRGB-encoded: decoded at first load as Rgba8UnormSrgb does
                                (texture.rs:36); intermediates are linear unorm8 (gpu_state.rs:608) */
-    NORM_CS_RAW = 1u        /* bytes/255 throughout (synthetic data) */
+    NORM_CS_RAW = 1u,       /* bytes/255 throughout (synthetic data) */
+    NORM_OUT_SRGB = 2u      /* or-ed in: the finished frame is sRGB-encoded as the reference's surface does on
+                               store (gpu_state.rs:94-99 picks the first sRGB surface format; texture.rs:36 is the
+                               matching decode at load), i.e. what a norm user sees on screen.  Accepted by
+                               norm_cuda_effects, norm_cuda_chain[_async|_host|_band*] and norm_cuda_band_step_async.
+                               RGB through an exact 256-entry table after the last stage, alpha untouched; the
+                               chain's SSIM is of the linear result.  One extra in-place pass (8 B/pixel). */
 };
 
 /* Decoded PNG as the reference's `Png` holds it (src/png/grammar.rs:65-70): header fields,
@@ -166,6 +172,13 @@ void norm_cuda_host_free(norm_ctx *ctx, void *p);
  * match).  NORM_E_UNSUPPORTED in compat mode for inputs the reference cannot expand. */
 norm_status norm_cuda_expand_rgba8(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, norm_img *out,
                                    uint32_t frame);
+/* As norm_cuda_expand_rgba8 with the scanlines already in DEVICE memory (png->pixels is a device pointer: the GPU
+ * unfilter's output, or a decoder that inflates on the device): `frames` images of one geometry, rows row_pitch
+ * bytes apart (a multiple of 16, base 16-byte aligned, and at least 48 readable bytes after the last row: the last
+ * item of a ragged row reads past it), images frame_stride bytes apart, into frames [frame0, frame0 + frames) of
+ * `out`.  ONE launch for the whole batch, asynchronous on the context's stream.  png->len is the length of one image. */
+norm_status norm_cuda_expand_rgba8_device(norm_ctx *ctx, const NormPngDesc *png, size_t row_pitch, size_t frame_stride,
+                                          uint32_t frames, int32_t mode, norm_img *out, uint32_t frame0);
 /* Same, result copied to a host buffer of 4*width*height bytes (the Cow<[u8]> the
  * reference returns). */
 norm_status norm_cuda_expand_rgba8_host(norm_ctx *ctx, const NormPngDesc *png, int32_t mode,
@@ -444,6 +457,8 @@ norm_status norm_cuda_ssim_static(const void *a_dev, const void *b_dev, uint32_t
 /* Normalised 1-D taps of the separable blur and the texel offset of tap 0
  * (image_shader.wgsl:81-103 under the floor convention). */
 norm_status norm_blur_taps(uint32_t radius, float *taps, int32_t *dmin);
+/* The table NORM_OUT_SRGB applies: code of a stored linear unorm8 byte under the surface's sRGB encode. */
+norm_status norm_srgb_encode_lut(uint8_t lut[256]);
 /* 256-entry front table: sRGB decode at load + gamma pass + unorm8 store. */
 norm_status norm_front_lut(uint32_t flags, uint32_t gamma, uint8_t lut[256]);
 /* sRGB tables of the shape render texture: eotf[k] = decoded value of code k; thresh[j] = linear

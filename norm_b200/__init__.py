@@ -5,7 +5,7 @@ host-side mirror of the reference's effect API over it.  Importing never builds 
 back: a missing extension raises at first use.
 """
 from ._lib import (LIB_PATH, NORM_CS_RAW, NORM_CS_REFERENCE, NORM_EXPAND_COMPAT, NORM_EXPAND_SPEC,
-                   NORM_MAX_BLUR_RADIUS, NormFeatureUniform, NormPngDesc, PROTOTYPES, load)
+                   NORM_MAX_BLUR_RADIUS, NORM_OUT_SRGB, NormFeatureUniform, NormPngDesc, PROTOTYPES, load)
 from .api import (Band, Circle, Context, DeviceImage, DrawUniform, EffectPipeline, EffectPipelineBuilder, FeatureUniform, NormError, Png,
                   Texture, blur_taps, front_lut, plan_band, plan_frames, reference_pipeline, ShapeUniform, srgb_tables,
                   ssim_from_moments)

@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libnorm_cuda.so")
 
 NORM_OK, NORM_E_INVALID_ARG, NORM_E_UNSUPPORTED, NORM_E_CUDA, NORM_E_NCCL, NORM_E_OOM, NORM_E_DIM_MISMATCH = range(7)
 NORM_CS_REFERENCE, NORM_CS_RAW = 0, 1
+NORM_OUT_SRGB = 2
 NORM_EXPAND_COMPAT, NORM_EXPAND_SPEC = 0, 1
 NORM_MAX_BLUR_RADIUS = 63
 
@@ -107,6 +108,7 @@ PROTOTYPES = {
     "norm_cuda_host_free": (None, [_vp, _vp]),
     "norm_cuda_expand_rgba8": (_i32, [_vp, C.POINTER(NormPngDesc), _i32, _vp, _u32]),
     "norm_cuda_expand_rgba8_host": (_i32, [_vp, C.POINTER(NormPngDesc), _i32, _vp]),
+    "norm_cuda_expand_rgba8_device": (_i32, [_vp, C.POINTER(NormPngDesc), _sz, _sz, _u32, _i32, _vp, _u32]),
     "norm_cuda_unfilter": (_i32, [_vp, C.POINTER(NormInflatedDesc), _vp]),
     "norm_cuda_unfilter_expand_rgba8": (_i32, [_vp, C.POINTER(NormInflatedDesc), _vp, _i32, _vp, _i32, _i32, _vp, _u32]),
     "norm_cuda_unfilter_expand_rgba8_batch": (_i32, [_vp, C.POINTER(NormInflatedDesc), _u32, _vp, _i32, _vp, _i32, _i32,
@@ -150,6 +152,7 @@ PROTOTYPES = {
     "norm_blur_taps": (_i32, [_u32, C.POINTER(C.c_float), C.POINTER(_i32)]),
     "norm_front_lut": (_i32, [_u32, _u32, C.POINTER(C.c_uint8)]),
     "norm_srgb_tables": (_i32, [C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "norm_srgb_encode_lut": (_i32, [C.POINTER(C.c_uint8)]),
     "norm_plan_band": (_i32, [_fu, _u32, _i32, _i32, C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_u32),
                               C.POINTER(_u32)]),
     "norm_plan_frames": (_i32, [_u32, _i32, _i32, C.POINTER(_u32), C.POINTER(_u32)]),

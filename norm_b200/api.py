@@ -283,6 +283,13 @@ class Context:
         d = png.desc()
         self._ok(self.lib.norm_cuda_expand_rgba8(self.h, C.byref(d), mode, out.handle, frame))
 
+    def expand_rgba8_device(self, png, device_ptr, row_pitch, frame_stride, frames, mode, out, frame0=0):
+        """Scanlines already in device memory (png supplies geometry / PLTE / tRNS); asynchronous, one launch."""
+        d = png.desc()
+        d.pixels = C.c_void_p(device_ptr)
+        d.len = row_pitch * png.height
+        self._ok(self.lib.norm_cuda_expand_rgba8_device(self.h, C.byref(d), row_pitch, frame_stride, frames, mode, out.handle, frame0))
+
     def expand_rgba8_host(self, png, mode):
         out = np.empty((png.height, png.width, 4), np.uint8)
         d = png.desc()

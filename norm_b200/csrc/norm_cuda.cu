@@ -19,6 +19,7 @@
 #include "chain_kernels.cuh"
 #include "chain2_kernels.cuh"
 #include "common.cuh"
+#include "expand_kernels.cuh"
 #include "filter_kernels.cuh"
 #include "overlay_kernels.cuh"
 #include "stencil_kernels.cuh"
@@ -315,6 +316,24 @@ void make_srgb_tables(float *eotf, float *thresh) {
     }
 }
 
+// The surface's linear -> sRGB encode (gpu_state.rs:94-99 picks an sRGB surface format, so every colour the fragment
+// stage returns is encoded on store): code of a stored linear unorm8 byte c = the code whose decision interval holds
+// c/255, found in the same threshold table the overlay uses (exact: no pow at run time).  Alpha is not encoded.
+void make_srgb_encode_lut(Lut256 &lut) {
+    float eotf[256], thresh[256];
+    make_srgb_tables(eotf, thresh);
+    for (int c = 0; c < 256; ++c) {
+        const float v = (float)c / 255.0f;
+        unsigned lo = 0, hi = 255;
+        while (lo < hi) {
+            const unsigned mid = (lo + hi + 1) >> 1;
+            if (v >= thresh[mid]) lo = mid;
+            else hi = mid - 1;
+        }
+        lut.v[c] = (uint8_t)lo;
+    }
+}
+
 norm_status copy_view(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const ImgView &out) {
     for (uint32_t f = 0; f < in.frames; ++f)
         CU_TRY(ctx, cudaMemcpy2DAsync(out.ptr + (size_t)f * out.frame_stride, out.pitch,
@@ -464,11 +483,24 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
     fp.out_y1 = slot.win_y1 ? std::min(slot.win_y1, in.h) : in.h;
     if (fp.out_y0 >= fp.out_y1) return fail(ctx, NORM_E_INVALID_ARG, "empty output row window");
     const uint32_t out_rows = fp.out_y1 - fp.out_y0;
-    // enough work items to fill the machine ~4 times over; bands no shorter than 64 rows
+    // Row bands per frame: the persistent grid takes ceil(items / slots) rounds of one item per CTA, and an item costs
+    // its rows plus a fixed pipeline fill (R - 1 extra rows of H pass and about one batch).  Pick the band count
+    // (bands no shorter than 64 rows) with the smallest rounds x item cost: one band when there are many frames, a
+    // count that fills the last round when one giant image gives only a few hundred strips.
     const size_t slots = (size_t)ctx->sm_count * per_sm;
     const size_t base_items = (size_t)fp.strips * in.frames;
-    uint32_t bands = (uint32_t)std::min<size_t>(std::max<size_t>(1, (4 * slots + base_items - 1) / base_items),
-                                                std::max<uint32_t>(1, out_rows / 64));
+    uint32_t bands = 1;
+    {
+        const uint32_t max_bands = std::max<uint32_t>(1, std::min<uint32_t>(out_rows / 64, 1024));
+        const uint64_t fill = (uint64_t)(R - 1) + C::RB;
+        uint64_t best = ~0ull;
+        for (uint32_t nbands = 1; nbands <= max_bands; ++nbands) {
+            const uint64_t rows_per = (out_rows + nbands - 1) / nbands;
+            const uint64_t rounds = (base_items * nbands + slots - 1) / slots;
+            const uint64_t cost = rounds * (rows_per + fill);
+            if (cost < best) best = cost, bands = nbands;
+        }
+    }
     fp.band_rows = (out_rows + bands - 1) / bands;
     fp.bands = (out_rows + fp.band_rows - 1) / fp.band_rows;
     fp.invert = p.inv ? 1u : 0u;
@@ -608,17 +640,30 @@ ImgView sub_rows(const ImgView &v, uint32_t y0, uint32_t y1) {
     return r;
 }
 
+// NORM_OUT_SRGB: one table pass over the finished frame, in place (RGB through the encode table, alpha kept).
+norm_status encode_srgb_inplace(norm_ctx *ctx, cudaStream_t s, const ImgView &v) {
+    static const Lut256 enc = [] {
+        Lut256 l;
+        make_srgb_encode_lut(l);
+        return l;
+    }();
+    return launch_front(ctx, s, v, v, enc, /*use_lut=*/true, /*gray=*/false, /*inv=*/false);
+}
+
 // Chain in -> out; SSIM (d_ssim) and/or raw moments (d_moments) over output rows [y0, y1) only.
 norm_status run_chain_rows(norm_ctx *ctx, Slot &slot, const NormFeatureUniform *f, uint32_t flags, const ImgView &in,
                            const ImgView &out, double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1) {
     const StagePlan p = make_plan(f, flags, /*chain=*/true);
     bool fused = false;
     NORM_TRY(try_launch_chain_fused(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1, &fused));
-    if (fused) return NORM_OK;
-    NORM_TRY(run_stages_unfused(ctx, slot, p, in, out));
-    if (d_ssim || d_moments)
-        NORM_TRY(launch_ssim(ctx, slot, sub_rows(out, y0, std::min(y1, in.h)), sub_rows(in, y0, std::min(y1, in.h)),
-                             d_moments, d_ssim));
+    if (!fused) {
+        NORM_TRY(run_stages_unfused(ctx, slot, p, in, out));
+        if (d_ssim || d_moments)
+            NORM_TRY(launch_ssim(ctx, slot, sub_rows(out, y0, std::min(y1, in.h)), sub_rows(in, y0, std::min(y1, in.h)),
+                                 d_moments, d_ssim));
+    }
+    // the SSIM above is of the linear result; the display encode comes last
+    if (flags & NORM_OUT_SRGB) NORM_TRY(encode_srgb_inplace(ctx, slot.stream, out));
     return NORM_OK;
 }
 
@@ -953,13 +998,23 @@ static bool valid_depth(int ct, int bd) {
     }
 }
 
+extern "C++" {
+template <int CT, int BD, int MODE>
+static void launch_expand(const ExpandParams &p, const ImgView &out, unsigned grid, cudaStream_t s) {
+    expand_kernel<CT, BD, MODE><<<grid, 256, 0, s>>>(p, out);
+}
+}
+
+// `nframes` images of one geometry -> frames [frame, frame + nframes) of `out`, ONE launch.  Host pixels (one image)
+// are uploaded to a 16-byte row pitch; device pixels (the unfilter's output) already have one.
 static norm_status expand_impl(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, const ImgView &out, uint32_t frame,
-                               bool pixels_on_device, size_t device_row_stride = 0) {
+                               bool pixels_on_device, size_t device_row_stride = 0, uint32_t nframes = 1,
+                               size_t device_frame_stride = 0) {
     if (!png || !png->pixels) return fail(ctx, NORM_E_INVALID_ARG, "png descriptor / pixels is NULL");
     const int ct = png->color_type, bd = png->bit_depth;
     if (!channels_of(ct) || !valid_depth(ct, bd)) return fail(ctx, NORM_E_INVALID_ARG, "invalid colour type / bit depth");
     if (png->width != out.w || png->height != out.h) return fail(ctx, NORM_E_DIM_MISMATCH, "image size differs from png");
-    if (frame >= out.frames) return fail(ctx, NORM_E_INVALID_ARG, "frame out of range");
+    if (nframes == 0 || (uint64_t)frame + nframes > out.frames) return fail(ctx, NORM_E_INVALID_ARG, "frame out of range");
     if (mode != NORM_EXPAND_COMPAT && mode != NORM_EXPAND_SPEC) return fail(ctx, NORM_E_INVALID_ARG, "unknown mode");
     if (mode == NORM_EXPAND_COMPAT && (bd != 8 || ct == 3))
         return fail(ctx, NORM_E_UNSUPPORTED,
@@ -972,17 +1027,22 @@ static norm_status expand_impl(norm_ctx *ctx, const NormPngDesc *png, int32_t mo
     const size_t rowb = ((size_t)png->width * channels_of(ct) * bd + 7) / 8;
     if (png->len < rowb * png->height) return fail(ctx, NORM_E_INVALID_ARG, "pixel buffer shorter than height*row_bytes");
 
-    if (!pixels_on_device) {
-        NORM_TRY(ensure_buf(ctx, ctx->raw, align_up(rowb * png->height, 256)));
-        CU_TRY(ctx, cudaMemcpyAsync(ctx->raw.p, png->pixels, rowb * png->height, cudaMemcpyHostToDevice, ctx->main.stream));
-    }
-
     ExpandParams p;
     std::memset(&p, 0, sizeof(p));
-    p.src = pixels_on_device ? png->pixels : static_cast<const uint8_t *>(ctx->raw.p);
-    p.src_row_bytes = (pixels_on_device && device_row_stride) ? device_row_stride : rowb;
-    p.w = png->width, p.h = png->height;
-    p.bit_depth = bd, p.color_type = ct, p.mode = mode;
+    if (!pixels_on_device) {
+        // rows re-pitched to 16 bytes on the way up, so every load of the kernel is aligned; 64 bytes of slack: the
+        // last item of a ragged row may read a few bytes past the row
+        const size_t pitch = align_up(rowb, 16);
+        NORM_TRY(ensure_buf(ctx, ctx->raw, align_up(pitch * png->height + 64, 256)));
+        CU_TRY(ctx, cudaMemcpy2DAsync(ctx->raw.p, pitch, png->pixels, rowb, rowb, png->height, cudaMemcpyHostToDevice,
+                                      ctx->main.stream));
+        p.src = static_cast<const uint8_t *>(ctx->raw.p), p.src_pitch = pitch, p.src_frame_stride = 0;
+    } else {
+        if (device_row_stride % 16 != 0 || ((uintptr_t)png->pixels & 15u) != 0)
+            return fail(ctx, NORM_E_INVALID_ARG, "device scanlines must have a 16-byte aligned base and pitch");
+        p.src = png->pixels, p.src_pitch = device_row_stride, p.src_frame_stride = device_frame_stride;
+    }
+    p.w = png->width, p.h = png->height, p.frames = nframes, p.frame0 = frame;
     if (png->plte && png->n_plte > 0) {
         std::memcpy(p.plte, png->plte, (size_t)png->n_plte * 3);
         p.n_plte = png->n_plte;
@@ -1002,9 +1062,31 @@ static norm_status expand_impl(norm_ctx *ctx, const NormPngDesc *png, int32_t mo
             p.has_key = 1;
         }
     }
-    const size_t items = (size_t)((png->width + 3) / 4) * png->height;
-    const unsigned grid = grid_for(ctx, (items + 255) / 256, 8);
-    expand_kernel<<<grid, 256, 0, ctx->main.stream>>>(p, out, frame);
+    const size_t items = (size_t)((png->width + 3) / 4) * png->height * nframes;
+    const unsigned grid = grid_for(ctx, (items + 511) / 512, 8);  // two items per thread and round
+    cudaStream_t s = ctx->main.stream;
+    // one instantiation per {colour type, bit depth, mode}: compat = 8-bit ct 0/2/4/6; spec = everything PngSuite has
+    bool launched = true;
+    if (mode == NORM_EXPAND_COMPAT) {
+        switch (ct) {
+        case 0: launch_expand<0, 8, 0>(p, out, grid, s); break;
+        case 2: launch_expand<2, 8, 0>(p, out, grid, s); break;
+        case 4: launch_expand<4, 8, 0>(p, out, grid, s); break;
+        case 6: launch_expand<6, 8, 0>(p, out, grid, s); break;
+        default: launched = false;
+        }
+    } else {
+        switch (ct * 100 + bd) {
+#define NORM_EXPAND_CASE(CT_, BD_) case CT_ * 100 + BD_: launch_expand<CT_, BD_, 1>(p, out, grid, s); break;
+            NORM_EXPAND_CASE(0, 1) NORM_EXPAND_CASE(0, 2) NORM_EXPAND_CASE(0, 4) NORM_EXPAND_CASE(0, 8) NORM_EXPAND_CASE(0, 16)
+            NORM_EXPAND_CASE(2, 8) NORM_EXPAND_CASE(2, 16)
+            NORM_EXPAND_CASE(3, 1) NORM_EXPAND_CASE(3, 2) NORM_EXPAND_CASE(3, 4) NORM_EXPAND_CASE(3, 8)
+            NORM_EXPAND_CASE(4, 8) NORM_EXPAND_CASE(4, 16) NORM_EXPAND_CASE(6, 8) NORM_EXPAND_CASE(6, 16)
+#undef NORM_EXPAND_CASE
+        default: launched = false;
+        }
+    }
+    if (!launched) return fail(ctx, NORM_E_INVALID_ARG, "invalid colour type / bit depth");
     LAUNCH_CHECK(ctx);
     return NORM_OK;
 }
@@ -1019,6 +1101,17 @@ norm_status norm_cuda_expand_rgba8(norm_ctx *ctx, const NormPngDesc *png, int32_
     NORM_TRY(expand_to(ctx, png, mode, out->v, frame));
     CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));  // png->pixels may be pageable: do not retain it
     return NORM_OK;
+}
+
+norm_status norm_cuda_expand_rgba8_device(norm_ctx *ctx, const NormPngDesc *png, size_t row_pitch, size_t frame_stride,
+                                          uint32_t frames, int32_t mode, norm_img *out, uint32_t frame0) {
+    NORM_TRY(bind(ctx));
+    if (!out) return fail(ctx, NORM_E_INVALID_ARG, "out is NULL");
+    if (!png) return fail(ctx, NORM_E_INVALID_ARG, "png descriptor is NULL");
+    const size_t rowb = ((size_t)png->width * channels_of(png->color_type) * png->bit_depth + 7) / 8;
+    if (row_pitch < rowb) return fail(ctx, NORM_E_INVALID_ARG, "row pitch shorter than a scanline");
+    if (frames > 1 && frame_stride < row_pitch * png->height) return fail(ctx, NORM_E_INVALID_ARG, "frame stride shorter than an image");
+    return expand_impl(ctx, png, mode, out->v, frame0, /*pixels_on_device=*/true, row_pitch, frames, frame_stride);
 }
 
 norm_status norm_cuda_expand_rgba8_host(norm_ctx *ctx, const NormPngDesc *png, int32_t mode, uint8_t *out_rgba8) {
@@ -1078,11 +1171,12 @@ static norm_status unfilter_to_device(norm_ctx *ctx, const NormInflatedDesc *des
             return fail(ctx, NORM_E_INVALID_ARG, "images of a batch must share width, height, bit depth, colour type and interlace");
         if (e.len != need) return fail(ctx, NORM_E_INVALID_ARG, "inflated length does not match the image geometry");
     }
-    const size_t out_bytes = rowb(w) * h;
+    const size_t raster_pitch = align_up(rowb(w), 16);   // de-interlaced rows at a 16-byte pitch, + slack for ragged reads
+    const size_t out_bytes = raster_pitch * h + 64;
     const size_t src_stride = align_up(need, 256), dst_stride = align_up(pass_bytes, 256), ft_stride = align_up(ft_bytes, 256),
                  raw_stride = align_up(out_bytes, 256);
     NORM_TRY(ensure_buf(ctx, ctx->inflated, src_stride * n));
-    NORM_TRY(ensure_buf(ctx, ctx->passes, (dst_stride + ft_stride) * n));
+    NORM_TRY(ensure_buf(ctx, ctx->passes, (dst_stride + ft_stride) * n + 64));  // + slack: expansion may read a few bytes past a ragged last row
     if (d->interlace) NORM_TRY(ensure_buf(ctx, ctx->raw, raw_stride * n));
     if (!ctx->d_status) CU_TRY(ctx, cudaMalloc(&ctx->d_status, sizeof(int32_t)));
     cudaStream_t s = ctx->main.stream;
@@ -1140,7 +1234,7 @@ static norm_status unfilter_to_device(norm_ctx *ctx, const NormInflatedDesc *des
                 else dq.pass_px[p] += i0 * dst_stride;
             }
             dq.dst = static_cast<uint8_t *>(ctx->raw.p) + i0 * raw_stride;
-            dq.w = w, dq.h = h, dq.row_bytes = (uint32_t)rowb(w), dq.bits = bits;
+            dq.w = w, dq.h = h, dq.row_bytes = (uint32_t)rowb(w), dq.bits = bits, dq.dst_pitch = (uint32_t)raster_pitch;
             dq.pass_stride = dst_stride, dq.dst_stride = raw_stride;
             const unsigned gdx = std::max(1u, grid_for(ctx, (out_bytes + 255) / 256, 8) / std::min<uint32_t>(cnt, 64u));
             deinterlace_kernel<<<dim3(gdx, cnt), 256, 0, s>>>(dq);
@@ -1148,7 +1242,7 @@ static norm_status unfilter_to_device(norm_ctx *ctx, const NormInflatedDesc *des
         }
     }
     if (d->interlace) {
-        *dev_out = static_cast<const uint8_t *>(ctx->raw.p), *pitch_out = rowb(w), *img_stride_out = raw_stride;
+        *dev_out = static_cast<const uint8_t *>(ctx->raw.p), *pitch_out = raster_pitch, *img_stride_out = raw_stride;
     } else {
         *dev_out = up.pass[0].dst, *pitch_out = up.pass[0].pitch, *img_stride_out = dst_stride;
     }
@@ -1185,10 +1279,8 @@ norm_status norm_cuda_unfilter_expand_rgba8_batch(norm_ctx *ctx, const NormInfla
     png.width = descs->width, png.height = descs->height, png.bit_depth = descs->bit_depth, png.color_type = descs->color_type;
     png.len = pitch * descs->height;
     png.plte = plte, png.n_plte = n_plte, png.trns = trns, png.n_trns = n_trns;
-    for (uint32_t i = 0; i < n; ++i) {
-        png.pixels = dev + (size_t)i * stride;
-        NORM_TRY(expand_impl(ctx, &png, mode, out->v, frame0 + i, /*pixels_on_device=*/true, pitch));
-    }
+    png.pixels = dev;  // the n unfiltered images sit `stride` bytes apart: one launch expands them all
+    NORM_TRY(expand_impl(ctx, &png, mode, out->v, frame0, /*pixels_on_device=*/true, pitch, n, stride));
     CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
     return NORM_OK;
 }
@@ -1264,6 +1356,7 @@ norm_status norm_cuda_effects(norm_ctx *ctx, const NormFeatureUniform *f, uint32
         flip_kernel<<<grid_for(ctx, (items + 255) / 256, 8), 256, 0, ctx->main.stream>>>(tmp, out->v, flip_x, flip_y);
         LAUNCH_CHECK(ctx);
     }
+    if (flags & NORM_OUT_SRGB) NORM_TRY(encode_srgb_inplace(ctx, ctx->main.stream, out->v));
     CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
     return NORM_OK;
 }
@@ -1627,6 +1720,14 @@ norm_status norm_blur_taps(uint32_t radius, float *taps, int32_t *dmin) {
 norm_status norm_srgb_tables(float eotf[256], float thresh[256]) {
     if (!eotf || !thresh) return NORM_E_INVALID_ARG;
     make_srgb_tables(eotf, thresh);
+    return NORM_OK;
+}
+
+norm_status norm_srgb_encode_lut(uint8_t lut[256]) {
+    if (!lut) return NORM_E_INVALID_ARG;
+    Lut256 l;
+    make_srgb_encode_lut(l);
+    std::memcpy(lut, l.v, 256);
     return NORM_OK;
 }
 

@@ -161,6 +161,7 @@ struct DeinterlaceParams {
     uint32_t pass_row_bytes[7];
     uint8_t *dst;               // raster rows
     uint32_t w, h, row_bytes, bits;  // bits per pixel
+    uint32_t dst_pitch;              // bytes between raster rows of dst (16-byte multiple: pixel expansion reads it aligned)
     size_t pass_stride, dst_stride;  // image blockIdx.y of a batch sits this far into the two buffers
 };
 
@@ -201,7 +202,7 @@ __global__ void __launch_bounds__(256) deinterlace_kernel(const __grid_constant_
                 outb |= v << (8 - p.bits - i * p.bits);
             }
         }
-        dst[it] = (uint8_t)outb;
+        dst[(size_t)y * p.dst_pitch + bx] = (uint8_t)outb;
     }
 }
 

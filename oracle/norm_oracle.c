@@ -868,6 +868,24 @@ static inline unsigned srgb_code(const float thresh[256], float v) {
     return lo;
 }
 
+/* Surface encode of a finished frame (gpu_state.rs:94-99: the colour target is the first sRGB surface format, so
+ * the value fs_main returns is sRGB-encoded on store; texture.rs:36 is the matching decode at load).  A stage
+ * output is a stored linear unorm8 byte c; its code is the one whose decision interval contains c/255. */
+void oracle_srgb_encode_lut(uint8_t lut[256]) {
+    float eotf[256], thresh[256];
+    oracle_srgb_tables(eotf, thresh);
+    for (int c = 0; c < 256; ++c) lut[c] = (uint8_t)srgb_code(thresh, (float)c / 255.0f);
+}
+
+void oracle_encode_srgb(const uint8_t *in, size_t npix, uint8_t *out) {
+    uint8_t lut[256];
+    oracle_srgb_encode_lut(lut);
+    for (size_t i = 0; i < npix; ++i) {
+        out[4 * i + 0] = lut[in[4 * i + 0]], out[4 * i + 1] = lut[in[4 * i + 1]], out[4 * i + 2] = lut[in[4 * i + 2]];
+        out[4 * i + 3] = in[4 * i + 3]; /* alpha is linear */
+    }
+}
+
 static inline float smoothstep_f(float e0, float e1, float x) {
     float t = (x - e0) / (e1 - e0);
     t = fminf(fmaxf(t, 0.0f), 1.0f);

@@ -104,6 +104,9 @@ typedef struct {
     float camera_view_proj[4][4];
 } oracle_draw_uniform;
 void oracle_srgb_tables(float eotf[256], float thresh[256]);
+/* gpu_state.rs:94-99: the sRGB surface's encode of a stored linear unorm8 byte (table) and of a whole RGBA8 frame */
+void oracle_srgb_encode_lut(uint8_t lut[256]);
+void oracle_encode_srgb(const uint8_t *in, size_t npix, uint8_t *out);
 int oracle_overlay(const uint8_t *in, uint32_t w, uint32_t h, const oracle_shape_uniform *su,
                    const oracle_circle *circles, const oracle_draw_uniform *du, uint8_t *out);
 

@@ -111,6 +111,10 @@ def lib():
             getattr(L, n).restype = None
         L.oracle_srgb_tables.argtypes = [f32p, f32p]
         L.oracle_srgb_tables.restype = None
+        L.oracle_srgb_encode_lut.argtypes = [u8p]
+        L.oracle_srgb_encode_lut.restype = None
+        L.oracle_encode_srgb.argtypes = [u8p, C.c_size_t, u8p]
+        L.oracle_encode_srgb.restype = None
         L.oracle_overlay.argtypes = [u8p, C.c_uint32, C.c_uint32, C.POINTER(ShapeUniform), C.POINTER(CircleData),
                                      C.POINTER(DrawUniform), u8p]
         for n in ("oracle_sharpen_s", "oracle_sharpen_r"):
@@ -289,6 +293,20 @@ def srgb_tables():
     e, t = np.zeros(256, np.float32), np.zeros(256, np.float32)
     lib().oracle_srgb_tables(e.ctypes.data_as(C.POINTER(C.c_float)), t.ctypes.data_as(C.POINTER(C.c_float)))
     return e, t
+
+
+def srgb_encode_lut():
+    lut = np.empty(256, np.uint8)
+    lib().oracle_srgb_encode_lut(_u8(lut))
+    return lut
+
+
+def encode_srgb(img):
+    """The surface's linear -> sRGB encode of a finished RGBA8 frame (or batch of frames)."""
+    img = np.ascontiguousarray(img, np.uint8)
+    out = np.empty_like(img)
+    lib().oracle_encode_srgb(_u8(img), img.size // 4, _u8(out))
+    return out
 
 
 def overlay(img, circles=(), selected=None, crosshair=None):

@@ -6,6 +6,8 @@ SSIM within 1e-5 absolute (we hold 1e-9).
 import glob
 import os
 
+import ctypes as C
+
 import numpy as np
 import pytest
 
@@ -227,6 +229,92 @@ def test_effects_reference_semantics(ctx, oracle, kw):
         for cs in (nb.NORM_CS_REFERENCE, nb.NORM_CS_RAW):
             got = run_stage(ctx, lambda s, d: ctx.effects(f, s, d, cs), img)[0]
             assert np.array_equal(got, oracle.effects(img, oracle_uniform(oracle, f), cs)), (kw, w, h, cs)
+
+
+def test_expand_device_resident_batch(ctx, oracle):
+    """norm_cuda_expand_rgba8_device: scanlines already in device memory at a 16-byte pitch, several images per
+    launch, every colour type / depth, ragged widths -- bit-exact against the oracle's expansion."""
+    import torch
+    rng = np.random.default_rng(77)
+    ch = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}
+    for (ct, bd) in [(0, 1), (0, 2), (0, 4), (0, 8), (0, 16), (2, 8), (2, 16), (3, 1), (3, 2), (3, 4), (3, 8), (4, 8), (4, 16), (6, 8), (6, 16)]:
+        for (w, h) in [(1, 1), (5, 3), (33, 7), (130, 9)]:
+            nf = 3
+            rowb = (w * ch[ct] * bd + 7) // 8
+            pitch = (rowb + 15) // 16 * 16
+            fstride = pitch * h + 64
+            host = rng.integers(0, 256, size=(nf, fstride), dtype=np.uint8)
+            plte = rng.integers(0, 256, size=3 * (1 << min(bd, 8)), dtype=np.uint8) if ct == 3 else None
+            trns = (rng.integers(0, 256, size=(1 << min(bd, 8)) // 2 + 1, dtype=np.uint8) if ct == 3 else
+                    np.array([0, host[0, 0] >> (8 - bd) if bd < 8 else host[0, 0]], np.uint8) if ct == 0 and bd <= 8 else None)
+            dev = torch.from_numpy(host).cuda()
+            torch.cuda.synchronize()
+            for mode in ([nb.NORM_EXPAND_SPEC] + ([nb.NORM_EXPAND_COMPAT] if bd == 8 and ct != 3 else [])):
+                out = ctx.image_create(w, h, nf + 1)
+                meta = nb.Png(w, h, bd, ct, np.zeros(1, np.uint8), plte=plte, trns=trns)
+                ctx.expand_rgba8_device(meta, dev.data_ptr(), pitch, fstride, nf, mode, out, 1)
+                ctx.sync()
+                got = out.download()
+                for i in range(nf):
+                    tight = np.ascontiguousarray(host[i, :pitch * h].reshape(h, pitch)[:, :rowb]).reshape(-1)
+                    d = oracle.DecodedPng.__new__(oracle.DecodedPng)
+                    d.__dict__.update(width=w, height=h, bit_depth=bd, color_type=ct, compression=0, filter=0, interlace=0, gamma=0,
+                                      pixels=tight, plte=plte if plte is not None else np.zeros(0, np.uint8),
+                                      trns=trns if trns is not None else np.zeros(0, np.uint8))
+                    exp = oracle.expand_rgba8(d, oracle.EXPAND_SPEC if mode == nb.NORM_EXPAND_SPEC else oracle.EXPAND_COMPAT)
+                    assert np.array_equal(got[1 + i], exp), (ct, bd, w, h, mode, i)
+                out.destroy()
+
+
+def test_surface_srgb_encode_on_output(ctx, oracle):
+    """NORM_OUT_SRGB: what a norm user sees is the fragment result sRGB-encoded by the surface
+    (gpu_state.rs:94-99).  The library's table is the oracle's; effects, chain, host chain and a banded step with
+    the flag equal the oracle's linear result put through it; alpha is untouched and the SSIM stays that of the
+    linear result."""
+    lut = (C.c_uint8 * 256)()
+    assert nb.load().norm_srgb_encode_lut(lut) == 0
+    assert np.array_equal(np.frombuffer(bytes(lut), np.uint8), oracle.srgb_encode_lut())
+    for (w, h) in [(5, 7), (130, 70), (333, 200)]:
+        img = smooth_rgba(w, h, seed=21)
+        for kw in (dict(), dict(grayscale=1, blur=1, blur_radius=21), dict(edge_detect=1), dict(blur=1, blur_radius=7, edge_detect=1),
+                   dict(blur=1, blur_radius=21, edge_detect=1)):
+            f = uniform(w, h, **kw)
+            for cs in (nb.NORM_CS_REFERENCE, nb.NORM_CS_RAW):
+                got = run_stage(ctx, lambda s, d: ctx.effects(f, s, d, cs | nb.NORM_OUT_SRGB), img)[0]
+                assert np.array_equal(got, oracle.encode_srgb(oracle.effects(img, oracle_uniform(oracle, f), cs))), (kw, w, h, cs)
+                src, dst = ctx.image_from_host(img[None]), ctx.image_create(w, h, 1)
+                s_lin = ctx.chain(f, src, dst, cs)
+                s_enc = ctx.chain(f, src, dst, cs | nb.NORM_OUT_SRGB)
+                eo, es = oracle.chain(img, oracle_uniform(oracle, f), cs)
+                assert np.array_equal(dst.download()[0], oracle.encode_srgb(eo)), (kw, w, h, cs)
+                assert s_lin[0] == s_enc[0] and abs(s_enc[0] - es) <= SSIM_TIGHT
+                hin, hout = np.ascontiguousarray(img[None]), np.empty((1, h, w, 4), np.uint8)
+                ctx.chain_host(f, hin, hout, 1, cs | nb.NORM_OUT_SRGB)
+                assert np.array_equal(hout[0], oracle.encode_srgb(eo))
+                src.destroy(), dst.destroy()
+    # banded: the owned rows come out encoded, whichever path (windowed or whole band) ran
+    w, h, nranks = 200, 150, 3
+    img = smooth_rgba(w, h, seed=22)
+    f = uniform(w, h, blur=1, blur_radius=21, edge_detect=1)
+    ctxs = [nb.Context(0) for _ in range(nranks)]
+    bands = [nb.Band(c, f, w, h, nranks, r) for r, c in enumerate(ctxs)]
+    handles = [b.export() for b in bands]
+    for b in bands:
+        b.connect(handles)
+        ext = np.zeros((b.src.height, w, 4), np.uint8)
+        ext[b.halo_up:b.halo_up + b.rows] = img[b.row0:b.row0 + b.rows]
+        b.src.upload(ext)
+        b.publish()
+    for b in bands:
+        b.step_async(nb.NORM_CS_RAW | nb.NORM_OUT_SRGB)
+    for b in bands:
+        b.sync()
+    got = np.concatenate([b.own_rows_of(b.dst) for b in bands])
+    assert np.array_equal(got, oracle.encode_srgb(oracle.chain(img, oracle_uniform(oracle, f), oracle.CS_RAW)[0]))
+    for b in bands:
+        b.destroy()
+    for c in ctxs:
+        c.close()
 
 
 CHAINS = [

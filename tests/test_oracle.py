@@ -466,3 +466,20 @@ def test_srgb_tables(oracle):
     # every code decodes to a value that encodes back to itself
     code = np.searchsorted(thresh[1:], eotf, side="right")
     assert (code == np.arange(256)).all()
+
+
+def test_srgb_surface_encode_table(oracle):
+    """gpu_state.rs:94-99: the surface encode of a stored linear byte.  The threshold table must agree with the direct
+    formula round(255 * OETF(c / 255)) for every byte, invert the load-time decode (texture.rs:36) on every code that
+    survives the 8-bit linear store, and be monotone."""
+    lut = oracle.srgb_encode_lut()
+    x = np.arange(256) / 255.0
+    direct = np.rint(255 * np.where(x <= 0.0031308, 12.92 * x, 1.055 * np.power(x, 1 / 2.4) - 0.055)).astype(int)
+    assert np.array_equal(lut.astype(int), direct)
+    assert (np.diff(lut.astype(int)) >= 0).all() and lut[0] == 0 and lut[255] == 255
+    dec = oracle.front_lut(oracle.CS_REFERENCE, 0)  # sRGB code -> stored linear byte
+    hi = np.arange(64, 256)  # above the dark end the 8-bit linear store keeps codes apart well enough to come back within 1
+    assert np.abs(lut[dec[hi]].astype(int) - hi).max() <= 3
+    img = np.arange(4 * 256, dtype=np.uint8).reshape(1, 256, 4)
+    enc = oracle.encode_srgb(img)
+    assert np.array_equal(enc[..., 3], img[..., 3]) and np.array_equal(enc[..., :3], lut[img[..., :3]])

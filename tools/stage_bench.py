@@ -75,6 +75,29 @@ rgb = np.random.default_rng(0).integers(0, 256, size=w8 * h8 * 3, dtype=np.uint8
 png = nb.Png(w8, h8, 8, 2, rgb)
 px = w8 * h8
 timeit("expand RGB8 8K (incl. H2D pageable)", lambda: ctx.expand_rgba8(png, nb.NORM_EXPAND_SPEC, out8, 0), 7, reps=3)
+# the expansion kernel itself: packed scanlines already in HBM (16-byte row pitch), 4 frames of 7680x4320 per launch,
+# against in_bpp/8 + 4 algorithmic bytes per pixel
+nf = 4
+out8b = ctx.image_create(w8, h8, nf)
+px = w8 * h8 * nf
+CH = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}
+for (name, ct, bd, mode) in (("RGBA8", 6, 8, nb.NORM_EXPAND_SPEC), ("RGB8", 2, 8, nb.NORM_EXPAND_SPEC), ("RGB8 compat", 2, 8, nb.NORM_EXPAND_COMPAT),
+                             ("gray8", 0, 8, nb.NORM_EXPAND_SPEC), ("gray+alpha8", 4, 8, nb.NORM_EXPAND_SPEC),
+                             ("palette8 + tRNS", 3, 8, nb.NORM_EXPAND_SPEC), ("gray4", 0, 4, nb.NORM_EXPAND_SPEC),
+                             ("palette2", 3, 2, nb.NORM_EXPAND_SPEC), ("gray1", 0, 1, nb.NORM_EXPAND_SPEC),
+                             ("gray16", 0, 16, nb.NORM_EXPAND_SPEC), ("RGB16", 2, 16, nb.NORM_EXPAND_SPEC), ("RGBA16", 6, 16, nb.NORM_EXPAND_SPEC)):
+    rowb8 = (w8 * CH[ct] * bd + 7) // 8
+    pitch8 = (rowb8 + 15) // 16 * 16
+    fstride = pitch8 * h8 + 256
+    buf = torch.randint(0, 256, (nf * fstride + 256,), dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    meta = nb.Png(w8, h8, bd, ct, np.zeros(1, np.uint8), plte=np.arange(768, dtype=np.uint8) if ct == 3 else None,
+                  trns=np.arange(200, dtype=np.uint8) if ct == 3 else None)
+    timeit(f"expand {name} 8K x{nf}, device-resident", lambda: ctx.expand_rgba8_device(meta, buf.data_ptr(), pitch8, fstride, nf, mode, out8b, 0),
+           CH[ct] * bd / 8 + 4, reps=5)
+    del buf
+out8b.destroy()
+px = w8 * h8
 
 # scanline unfilter (GPU wavefront) vs the host: a 1920x1080 RGB8 stream with all five filter types
 import time
