@@ -256,7 +256,9 @@ norm_status norm_cuda_chain_async(norm_ctx *ctx, const NormFeatureUniform *f, ui
 
 /* Host-buffer form of norm_cuda_chain: `frames` RGBA8 frames in host memory in, RGBA8 out
  * (tightly packed, 4*width bytes per row).  Uploads, runs and downloads in overlapping
- * chunks on the context's copy streams.  Use pinned buffers for full PCIe speed. */
+ * chunks on three internal streams of the context (NOT the context's own stream: a context created with
+ * norm_cuda_create_on_stream does not see this work on its stream).  Fully synchronous: on return, and on failure
+ * too, no copy into or out of the caller's buffers is still in flight.  Use pinned buffers for full PCIe speed. */
 norm_status norm_cuda_chain_host(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags,
                                  const uint8_t *in_rgba8, uint8_t *out_rgba8, uint32_t frames,
                                  double *ssim);
@@ -415,6 +417,15 @@ norm_status norm_cuda_overlay(norm_ctx *ctx, const NormShapeUniform *shapes, con
  * branch, ssim.rs:65-81): one global-window SSIM per frame, a[i] against b[i].
  * NORM_E_DIM_MISMATCH if geometries differ (ssim.rs:92-95).  ssim: `frames` doubles. */
 norm_status norm_cuda_ssim(norm_ctx *ctx, const norm_img *a, const norm_img *b, double *ssim);
+/* Png::compute_sim for images of any colour type: Png::luma_buffer picks the luma by colour type
+ * (src/png/ssim.rs:18-87) and the two images may differ in it.  `a` / `b` hold the RGBA8 expansion. */
+enum {
+    NORM_LUMA_RGB = 0,       /* RGB / RGBA: r*0.29891 + g*0.58661 + b*0.11448 on raw bytes (ssim.rs:56-58, 73-75) */
+    NORM_LUMA_GRAY = 1,      /* Grayscale: the sample itself (ssim.rs:25) */
+    NORM_LUMA_GRAY_UNIT = 2  /* GrayscaleAlpha: sample / 255.0 (ssim.rs:41: the reference mixes scales; kept) */
+};
+norm_status norm_cuda_ssim_luma(norm_ctx *ctx, const norm_img *a, int32_t luma_a, const norm_img *b, int32_t luma_b,
+                                double *ssim);
 /* The five raw moments per frame {sum x, sum y, sum x^2, sum y^2, sum xy} of the f32 lumas,
  * accumulated in f64 -- what a multi-GPU caller all-reduces before finalising.
  * moments: host array of 5*frames doubles. */

@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libnorm_cuda.so")
 NORM_OK, NORM_E_INVALID_ARG, NORM_E_UNSUPPORTED, NORM_E_CUDA, NORM_E_NCCL, NORM_E_OOM, NORM_E_DIM_MISMATCH = range(7)
 NORM_CS_REFERENCE, NORM_CS_RAW = 0, 1
 NORM_OUT_SRGB = 2
+NORM_LUMA_RGB, NORM_LUMA_GRAY, NORM_LUMA_GRAY_UNIT = 0, 1, 2
 NORM_EXPAND_COMPAT, NORM_EXPAND_SPEC = 0, 1
 NORM_MAX_BLUR_RADIUS = 63
 
@@ -147,6 +148,7 @@ PROTOTYPES = {
                                  C.POINTER(NormDrawUniform), _vp, _vp]),
     "norm_cuda_ssim": (_i32, [_vp, _vp, _vp, _dp]),
     "norm_cuda_ssim_moments": (_i32, [_vp, _vp, _vp, _dp]),
+    "norm_cuda_ssim_luma": (_i32, [_vp, _vp, _i32, _vp, _i32, _dp]),
     "norm_ssim_from_moments": (C.c_double, [_dp, C.c_double]),
     "norm_cuda_ssim_static": (_i32, [_vp, _vp, _u32, _u32, _u32, _sz, _sz, _vp, _vp, _vp]),
     "norm_blur_taps": (_i32, [_u32, C.POINTER(C.c_float), C.POINTER(_i32)]),

@@ -163,14 +163,24 @@ class Png:
         """ImageExt::rgba8 (grammar.rs:123-155), computed on the GPU."""
         return ctx.expand_rgba8_host(self, mode)
 
+    def luma_mode(self):
+        """The branch of Png::luma_buffer (ssim.rs:18-87) this image's colour type takes."""
+        if self.color_type in (2, 6):
+            return _lib.NORM_LUMA_RGB
+        if self.color_type == 0:
+            return _lib.NORM_LUMA_GRAY
+        if self.color_type == 4:
+            return _lib.NORM_LUMA_GRAY_UNIT
+        raise NormError(_lib.NORM_E_UNSUPPORTED, "luma buffer of a palette image: unimplemented in the reference (ssim.rs:83-86)")
+
     def compute_sim(self, reference_image, ctx, mode=NORM_EXPAND_COMPAT):
-        """Png::compute_sim (ssim.rs:91-106): `self` is the test image."""
+        """Png::compute_sim (ssim.rs:91-106): `self` is the test image; each image's luma follows its colour type."""
         if self.dimensions() != reference_image.dimensions():
             raise NormError(_lib.NORM_E_DIM_MISMATCH,
                             "Expect reference and test images to have identical dimensions.")
         a, b = Texture.from_image(ctx, self, mode), Texture.from_image(ctx, reference_image, mode)
         try:
-            return float(ctx.ssim(a.image, b.image)[0])
+            return float(ctx.ssim_luma(a.image, self.luma_mode(), b.image, reference_image.luma_mode())[0])
         finally:
             a.destroy(), b.destroy()
 
@@ -428,6 +438,11 @@ class Context:
     def ssim(self, a, b):
         s = np.zeros(a.frames, np.float64)
         self._ok(self.lib.norm_cuda_ssim(self.h, a.handle, b.handle, s.ctypes.data_as(C.POINTER(C.c_double))))
+        return s
+
+    def ssim_luma(self, a, luma_a, b, luma_b):
+        s = np.zeros(a.frames, np.float64)
+        self._ok(self.lib.norm_cuda_ssim_luma(self.h, a.handle, luma_a, b.handle, luma_b, s.ctypes.data_as(C.POINTER(C.c_double))))
         return s
 
     def ssim_moments(self, a, b):

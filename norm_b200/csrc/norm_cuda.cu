@@ -80,6 +80,7 @@ struct norm_ctx {
     DevBuf results;     // per-frame moments (5) + ssim (1), doubles
     double *h_results = nullptr;
     size_t h_results_cap = 0;
+    size_t chunk_bytes = 0;      // NORM_CUDA_CHUNK_BYTES: frames per chunk of the staged paths (tests: many small chunks)
     int fused_gen = 0;           // NORM_CUDA_FUSED_GEN=1 forces the first-generation fused kernel
     bool force_unfused = false;  // NORM_CUDA_FORCE_UNFUSED=1: run the chain as separate stage kernels
 };
@@ -344,7 +345,7 @@ norm_status copy_view(norm_ctx *ctx, cudaStream_t s, const ImgView &in, const Im
 
 // SSIM of a[i] vs b[i]; d_moments / d_ssim are device arrays (5*frames / frames) or NULL.
 norm_status launch_ssim(norm_ctx *ctx, Slot &slot, const ImgView &a, const ImgView &b, double *d_moments,
-                        double *d_ssim) {
+                        double *d_ssim, int luma_a = 0, int luma_b = 0) {
     const size_t chunks = (size_t)((a.w + 3) / 4) * a.h;
     size_t want = ((size_t)ctx->sm_count * 8 + a.frames - 1) / a.frames;  // ~8 CTAs per SM in total
     const size_t max_useful = (chunks + 256 * 4 - 1) / (256 * 4);
@@ -354,8 +355,16 @@ norm_status launch_ssim(norm_ctx *ctx, Slot &slot, const ImgView &a, const ImgVi
     // grid.y is limited to 65535: walk the batch in slices
     for (uint32_t f0 = 0; f0 < a.frames; f0 += 65535u) {
         const uint32_t n = std::min(65535u, a.frames - f0);
-        ssim_moments_kernel<<<dim3(bpf, n), 256, 0, slot.stream>>>(sub_frames(a, f0, n), sub_frames(b, f0, n),
-                                                                    partials + (size_t)f0 * bpf * 5);
+        const ImgView va = sub_frames(a, f0, n), vb = sub_frames(b, f0, n);
+        double *pp = partials + (size_t)f0 * bpf * 5;
+        const dim3 grid(bpf, n);
+        switch (luma_a * 3 + luma_b) {  // Png::luma_buffer's branch of each image (ssim.rs:18-87)
+#define NORM_SSIM_CASE(A_, B_) case A_ * 3 + B_: ssim_moments_kernel<A_, B_><<<grid, 256, 0, slot.stream>>>(va, vb, pp); break;
+            NORM_SSIM_CASE(0, 0) NORM_SSIM_CASE(0, 1) NORM_SSIM_CASE(0, 2) NORM_SSIM_CASE(1, 0) NORM_SSIM_CASE(1, 1)
+            NORM_SSIM_CASE(1, 2) NORM_SSIM_CASE(2, 0) NORM_SSIM_CASE(2, 1) NORM_SSIM_CASE(2, 2)
+#undef NORM_SSIM_CASE
+        default: return fail(ctx, NORM_E_INVALID_ARG, "unknown luma mode");
+        }
         LAUNCH_CHECK(ctx);
     }
     ssim_finalize_kernel<<<a.frames, 256, 0, slot.stream>>>(partials, bpf, (double)a.w * (double)a.h, d_moments,
@@ -415,7 +424,8 @@ norm_status run_stages_unfused(norm_ctx *ctx, Slot &slot, const StagePlan &p, co
     const size_t frame_bytes = align_up((size_t)in.w * 4, 256) * in.h;
     uint32_t chunk = in.frames;
     if (n > 1) {
-        chunk = (uint32_t)std::max<size_t>(1, std::min<size_t>(in.frames, ((size_t)256 << 20) / frame_bytes));
+        const size_t budget = ctx->chunk_bytes ? ctx->chunk_bytes : ((size_t)256 << 20);
+        chunk = (uint32_t)std::max<size_t>(1, std::min<size_t>(in.frames, budget / frame_bytes));
         NORM_TRY(ensure_buf(ctx, slot.tmp[0], frame_bytes * chunk));
         if (n > 2) NORM_TRY(ensure_buf(ctx, slot.tmp[1], frame_bytes * chunk));
     }
@@ -466,6 +476,20 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
     else if constexpr (GEN == 2) kern = chain_fused2_kernel<R, GRAY, FRONT, 0>;
     else kern = chain_fused_kernel<R, GRAY, FRONT>;
     constexpr int kThreads = GEN == 1 ? kFusedThreads : kC2Threads;
+    if constexpr (GEN != 1) {
+        // The pipelined kernel re-divides its registers between the warp groups (setmaxnreg) on the assumption that it
+        // was launched with exactly 80 per thread: with fewer, the groups that ask for more would wait forever for
+        // registers nobody releases.  Checked once per instantiation instead of trusted.
+        static int regs = -1;  // (per template instantiation)
+        if (regs < 0) {
+            cudaFuncAttributes fa;
+            CU_TRY(ctx, cudaFuncGetAttributes(&fa, kern));
+            regs = fa.numRegs;
+        }
+        if (regs != 80)
+            return fail(ctx, NORM_E_UNSUPPORTED, "fused kernel was built with " + std::to_string(regs) +
+                        " registers per thread; its setmaxnreg budgets need exactly 80 (check the nvcc flags)");
+    }
     CU_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kSmem));
     int per_sm = 1;
     CU_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, C::kSmem));
@@ -720,6 +744,7 @@ norm_status create_impl(int32_t device, void *ext_stream, bool use_ext, norm_ctx
     ctx->device = device;
     if (const char *e = std::getenv("NORM_CUDA_FORCE_UNFUSED")) ctx->force_unfused = e[0] == '1';
     if (const char *e = std::getenv("NORM_CUDA_FUSED_GEN")) ctx->fused_gen = std::atoi(e);
+    if (const char *e = std::getenv("NORM_CUDA_CHUNK_BYTES")) ctx->chunk_bytes = (size_t)std::strtoull(e, nullptr, 10);
     auto bail = [&](cudaError_t ce, const char *what) {
         g_create_error = std::string(what) + ": " + cudaGetErrorString(ce);
         norm_cuda_destroy(ctx);
@@ -1402,19 +1427,29 @@ norm_status norm_cuda_chain_host(norm_ctx *ctx, const NormFeatureUniform *f, uin
 
     // chunk: ~64 MB of frames per stage buffer, at least 1 frame; three chunks in flight
     const size_t frame_bytes = probe.frame_stride, host_frame = (size_t)w * 4 * h;
-    const uint32_t chunk = (uint32_t)std::max<size_t>(1, std::min<size_t>(frames, ((size_t)64 << 20) / frame_bytes));
+    const size_t budget = ctx->chunk_bytes ? ctx->chunk_bytes : ((size_t)64 << 20);
+    const uint32_t chunk = (uint32_t)std::max<size_t>(1, std::min<size_t>(frames, budget / frame_bytes));
     for (auto &s : ctx->pipe) {
         NORM_TRY(ensure_buf(ctx, s.stage_in, frame_bytes * chunk));
         NORM_TRY(ensure_buf(ctx, s.stage_out, frame_bytes * chunk));
     }
+    // From the first enqueue on, a failure must not return while copies into / out of the caller's buffers are
+    // still in flight on the pipe streams: drain them first, then report.
+    norm_status st = NORM_OK;
     uint32_t ci = 0;
-    for (uint32_t f0 = 0; f0 < frames; f0 += chunk, ++ci) {
+    for (uint32_t f0 = 0; f0 < frames && st == NORM_OK; f0 += chunk, ++ci) {
         Slot &s = ctx->pipe[ci % 3];
         const uint32_t nf = std::min(chunk, frames - f0);
         const ImgView vin = view_of(s.stage_in.p, w, h, nf), vout = view_of(s.stage_out.p, w, h, nf);
-        NORM_TRY(copy_frames(ctx, s.stream, vin, 0, nf, const_cast<uint8_t *>(in_rgba8) + (size_t)f0 * host_frame, 0, true));
-        NORM_TRY(run_chain(ctx, s, f, flags, vin, vout, d_ssim ? d_ssim + f0 : nullptr));
-        NORM_TRY(copy_frames(ctx, s.stream, vout, 0, nf, out_rgba8 + (size_t)f0 * host_frame, 0, false));
+        st = copy_frames(ctx, s.stream, vin, 0, nf, const_cast<uint8_t *>(in_rgba8) + (size_t)f0 * host_frame, 0, true);
+        if (st == NORM_OK) st = run_chain(ctx, s, f, flags, vin, vout, d_ssim ? d_ssim + f0 : nullptr);
+        if (st == NORM_OK) st = copy_frames(ctx, s.stream, vout, 0, nf, out_rgba8 + (size_t)f0 * host_frame, 0, false);
+    }
+    if (st != NORM_OK) {
+        const std::string why = ctx->err;
+        for (auto &s : ctx->pipe) cudaStreamSynchronize(s.stream);
+        (void)cudaGetLastError();
+        return fail(ctx, st, why);
     }
     for (auto &s : ctx->pipe) CU_TRY(ctx, cudaStreamSynchronize(s.stream));
     if (ssim) {
@@ -1591,13 +1626,14 @@ norm_status norm_cuda_sharpen(norm_ctx *ctx, uint32_t factor, const norm_img *in
 
 // ---- SSIM ------------------------------------------------------------------------------
 
-static norm_status ssim_impl(norm_ctx *ctx, const norm_img *a, const norm_img *b, double *moments, double *ssim) {
+static norm_status ssim_impl(norm_ctx *ctx, const norm_img *a, const norm_img *b, double *moments, double *ssim,
+                             int luma_a = 0, int luma_b = 0) {
     NORM_TRY(bind(ctx));
     NORM_TRY(check_pair(ctx, a, b, true));
     const uint32_t n = a->v.frames;
     NORM_TRY(ensure_results(ctx, n));
     double *d_m = static_cast<double *>(ctx->results.p), *d_s = d_m + (size_t)n * 5;
-    NORM_TRY(launch_ssim(ctx, ctx->main, a->v, b->v, d_m, d_s));
+    NORM_TRY(launch_ssim(ctx, ctx->main, a->v, b->v, d_m, d_s, luma_a, luma_b));
     CU_TRY(ctx, cudaMemcpyAsync(ctx->h_results, d_m, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost,
                                 ctx->main.stream));
     CU_TRY(ctx, cudaStreamSynchronize(ctx->main.stream));
@@ -1609,6 +1645,12 @@ static norm_status ssim_impl(norm_ctx *ctx, const norm_img *a, const norm_img *b
 norm_status norm_cuda_ssim(norm_ctx *ctx, const norm_img *a, const norm_img *b, double *ssim) {
     if (ctx && !ssim) return fail(ctx, NORM_E_INVALID_ARG, "ssim is NULL");
     return ssim_impl(ctx, a, b, nullptr, ssim);
+}
+
+norm_status norm_cuda_ssim_luma(norm_ctx *ctx, const norm_img *a, int32_t luma_a, const norm_img *b, int32_t luma_b, double *ssim) {
+    if (ctx && !ssim) return fail(ctx, NORM_E_INVALID_ARG, "ssim is NULL");
+    if (luma_a < 0 || luma_a > 2 || luma_b < 0 || luma_b > 2) return fail(ctx, NORM_E_INVALID_ARG, "unknown luma mode");
+    return ssim_impl(ctx, a, b, nullptr, ssim, luma_a, luma_b);
 }
 
 norm_status norm_cuda_ssim_moments(norm_ctx *ctx, const norm_img *a, const norm_img *b, double *moments) {
@@ -1698,7 +1740,7 @@ norm_status norm_cuda_ssim_static(const void *a_dev, const void *b_dev, uint32_t
     want = std::min(want, ((size_t)1184 + frames - 1) / frames);
     const uint32_t bpf = (uint32_t)std::max<size_t>(1, want);
     cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
-    ssim_moments_kernel<<<dim3(bpf, frames), 256, 0, s>>>(a, b, scratch);
+    ssim_moments_kernel<0, 0><<<dim3(bpf, frames), 256, 0, s>>>(a, b, scratch);
     if ((e = cudaGetLastError()) != cudaSuccess)
         return static_fail(NORM_E_CUDA, std::string("norm_cuda_ssim_static: launch: ") + cudaGetErrorString(e));
     ssim_finalize_kernel<<<frames, 256, 0, s>>>(scratch, bpf, (double)width * (double)height, moments_dev, ssim_dev);

@@ -994,6 +994,27 @@ double oracle_ssim_from_moments(const double m[5], double n) {
     return lum * con * str;                                                /* :136 */
 }
 
+/* Png::luma_buffer per colour type (ssim.rs:18-87), on the RGBA8 expansion of the image:
+ *   mode 0  RGB / RGBA        r*0.29891 + g*0.58661 + b*0.11448 on raw bytes   (:56-58, :73-75)
+ *   mode 1  Grayscale         y as f32                                            (:25)
+ *   mode 2  GrayscaleAlpha    y as f32 / 255.0  -- the reference's own inconsistency (:41), kept */
+static inline float luma_mode(const uint8_t *p, int mode) {
+    if (mode == 1) return (float)p[0];
+    if (mode == 2) return (float)p[0] / 255.0f;
+    return luma_ssim(p);
+}
+
+double oracle_ssim_luma(const uint8_t *a, const uint8_t *b, size_t npix, int mode_a, int mode_b) {
+    double sx = 0, sy = 0, sxx = 0, syy = 0, sxy = 0;
+#pragma omp parallel for schedule(static) reduction(+ : sx, sy, sxx, syy, sxy)
+    for (size_t i = 0; i < npix; ++i) {
+        const double x = (double)luma_mode(a + 4 * i, mode_a), y = (double)luma_mode(b + 4 * i, mode_b);
+        sx += x, sy += y, sxx += x * x, syy += y * y, sxy += x * y;
+    }
+    const double m[5] = {sx, sy, sxx, syy, sxy};
+    return oracle_ssim_from_moments(m, (double)npix);
+}
+
 double oracle_ssim(const uint8_t *a, const uint8_t *b, size_t npix) {
     double m[5];
     oracle_ssim_moments(a, b, npix, m);

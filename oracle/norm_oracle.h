@@ -115,6 +115,8 @@ int oracle_overlay(const uint8_t *in, uint32_t w, uint32_t h, const oracle_shape
 void oracle_ssim_moments(const uint8_t *a, const uint8_t *b, size_t npix, double m[5]);
 double oracle_ssim_from_moments(const double m[5], double npix);
 double oracle_ssim(const uint8_t *a, const uint8_t *b, size_t npix);
+/* per-colour-type lumas of Png::luma_buffer (ssim.rs:18-87): 0 RGB weights, 1 gray byte, 2 gray byte / 255 */
+double oracle_ssim_luma(const uint8_t *a, const uint8_t *b, size_t npix, int mode_a, int mode_b);
 /* Literal sequential-f32 evaluation, pass structure of ssim.rs:18-183 (reported, not a target). */
 float oracle_ssim_f32_literal(const uint8_t *a, const uint8_t *b, size_t npix);
 

@@ -126,6 +126,8 @@ def lib():
         L.oracle_ssim_from_moments.restype = C.c_double
         L.oracle_ssim.argtypes = [u8p, u8p, C.c_size_t]
         L.oracle_ssim.restype = C.c_double
+        L.oracle_ssim_luma.argtypes = [u8p, u8p, C.c_size_t, C.c_int, C.c_int]
+        L.oracle_ssim_luma.restype = C.c_double
         L.oracle_ssim_f32_literal.argtypes = [u8p, u8p, C.c_size_t]
         L.oracle_ssim_f32_literal.restype = C.c_float
         L.oracle_effects.argtypes = [C.POINTER(FeatureUniform), C.c_int, u8p, u8p]
@@ -341,6 +343,12 @@ def ssim(a, b):
     a, b = _img(a), _img(b)
     assert a.shape == b.shape
     return lib().oracle_ssim(_u8(a), _u8(b), a.shape[0] * a.shape[1])
+
+
+def ssim_luma(a, b, mode_a, mode_b):
+    a, b = _img(a), _img(b)
+    assert a.shape == b.shape
+    return lib().oracle_ssim_luma(_u8(a), _u8(b), a.shape[0] * a.shape[1], mode_a, mode_b)
 
 
 def ssim_f32_literal(a, b):

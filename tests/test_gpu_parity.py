@@ -231,6 +231,29 @@ def test_effects_reference_semantics(ctx, oracle, kw):
             assert np.array_equal(got, oracle.effects(img, oracle_uniform(oracle, f), cs)), (kw, w, h, cs)
 
 
+def test_compute_sim_follows_the_colour_type(ctx, oracle):
+    """Png::compute_sim (ssim.rs:91-106): the luma of each image is the branch of luma_buffer its colour type
+    takes (ssim.rs:18-87) -- RGB weights, the gray byte, or gray byte / 255 for gray + alpha -- and the two images
+    may differ in it.  Palette images raise, as the reference's `unimplemented!` does."""
+    rng = np.random.default_rng(5)
+    w, h = 97, 61
+    mk = {0: lambda: rng.integers(0, 256, size=w * h, dtype=np.uint8), 2: lambda: rng.integers(0, 256, size=w * h * 3, dtype=np.uint8),
+          4: lambda: rng.integers(0, 256, size=w * h * 2, dtype=np.uint8), 6: lambda: rng.integers(0, 256, size=w * h * 4, dtype=np.uint8)}
+    mode_of = {0: 1, 2: 0, 4: 2, 6: 0}
+    for ct_a in (0, 2, 4, 6):
+        for ct_b in (0, 2, 4, 6):
+            a, b = nb.Png(w, h, 8, ct_a, mk[ct_a]()), nb.Png(w, h, 8, ct_b, mk[ct_b]())
+            got = a.compute_sim(b, ctx)
+            ea, eb = a.rgba8(ctx), b.rgba8(ctx)
+            assert abs(got - oracle.ssim_luma(ea, eb, mode_of[ct_a], mode_of[ct_b])) <= SSIM_TIGHT, (ct_a, ct_b)
+    ga = nb.Png(w, h, 8, 4, mk[4]())
+    assert abs(ga.compute_sim(ga, ctx) - 1.0) < 1e-9                        # identical images: 1 whatever the scale
+    with pytest.raises(nb.NormError):
+        nb.Png(4, 4, 8, 3, np.zeros(16, np.uint8), plte=np.zeros(6, np.uint8)).compute_sim(ga, ctx)
+    with pytest.raises(nb.NormError):
+        ga.compute_sim(nb.Png(w + 1, h, 8, 4, np.zeros((w + 1) * h * 2, np.uint8)), ctx)   # ensure! on the dimensions
+
+
 def test_expand_device_resident_batch(ctx, oracle):
     """norm_cuda_expand_rgba8_device: scanlines already in device memory at a 16-byte pitch, several images per
     launch, every colour type / depth, ragged widths -- bit-exact against the oracle's expansion."""
@@ -364,6 +387,27 @@ def test_chain_host_pipeline(ctx, oracle):
     ctx.host_free(ph), ctx.host_free(poh)
 
 
+def test_multi_chunk_paths_bit_exact(oracle, monkeypatch):
+    """The chunk loops only large batches reach: the host pipeline's slot reuse (chunk index mod 3) and the unfused
+    chain's ping-pong temporaries rotating across chunks.  NORM_CUDA_CHUNK_BYTES (read when a context is created)
+    shrinks the chunk to one frame, so 11 frames make 11 chunks; outputs and SSIM must still equal the oracle."""
+    w, h, n = 160, 90, 11
+    monkeypatch.setenv("NORM_CUDA_CHUNK_BYTES", str(160 * 4 * 90 + 256 * 90))  # one (pitched) frame per chunk
+    frames = np.stack([smooth_rgba(w, h, seed=40 + i) for i in range(n)])
+    with nb.Context(0) as c:
+        for kw in (dict(blur=1, blur_radius=21, edge_detect=1),                            # fused kernel per chunk
+                   dict(invert=1, blur=1, blur_radius=7, sharpen=1, edge_detect=1)):       # four unfused stages per chunk
+            f = uniform(w, h, **kw)
+            eo, es = oracle.chain_batch(frames, oracle_uniform(oracle, f), oracle.CS_RAW)
+            out = np.empty_like(frames)
+            s = c.chain_host(f, frames, out, n, nb.NORM_CS_RAW)
+            assert np.array_equal(out, eo) and np.abs(s - es).max() <= SSIM_TIGHT, kw
+            src, dst = c.image_from_host(frames), c.image_create(w, h, n)
+            s = c.chain(f, src, dst, nb.NORM_CS_RAW)
+            assert np.array_equal(dst.download(), eo) and np.abs(s - es).max() <= SSIM_TIGHT, kw
+            src.destroy(), dst.destroy()
+
+
 def test_uniform_validation(ctx):
     src, dst = ctx.image_from_host(splitmix_rgba(16, 8)), ctx.image_create(16, 8, 1)
     with pytest.raises(nb.NormError) as e:
@@ -422,27 +466,44 @@ def test_config2_pngsuite_sobel(ctx, oracle):
         out.destroy(), tex.destroy()
 
 
-def test_config3_8k_chain_properties(ctx, oracle):
-    """configs[2] at full size (7680x4320): oracle on sampled row bands + size-independent properties."""
+def periodic_table_8k(oracle):
+    """BASELINE.md config 3, real content: the reference's tests/Periodic_table_large.png (6000x3300 RGBA8, decoded by
+    the oracle's PNG front-end) tiled with wrap-around to 7680x4320."""
+    d = oracle.png_decode(open(os.path.join(GOLDEN, "images", "Periodic_table_large.png"), "rb").read())
+    tile = oracle.expand_rgba8(d, oracle.EXPAND_SPEC)
+    assert tile.shape == (3300, 6000, 4)
+    ys, xs = np.arange(4320) % 3300, np.arange(7680) % 6000
+    return np.ascontiguousarray(tile[ys][:, xs])
+
+
+@pytest.mark.parametrize("content", ["prng", "periodic_table"])
+def test_config3_8k_chain_properties(ctx, oracle, content):
+    """configs[2] at full size (7680x4320), on the PRNG image and on the tiled periodic table, for every radius of the
+    BASELINE sweep: oracle on sampled row bands (top edge, middle, bottom edge) + size-independent properties."""
     w, h = 7680, 4320
-    img = splitmix_rgba(w, h, alpha=255)
-    yy = (np.arange(h, dtype=np.int64)[:, None] * 255 // (h - 1)).astype(np.uint8)
-    img[..., 0] = (img[..., 0].astype(np.uint16) + yy) // 2   # gradient so blur output is not flat
+    if content == "prng":
+        img = splitmix_rgba(w, h, alpha=255)
+        yy = (np.arange(h, dtype=np.int64)[:, None] * 255 // (h - 1)).astype(np.uint8)
+        img[..., 0] = (img[..., 0].astype(np.uint16) + yy) // 2   # gradient so blur output is not flat
+    else:
+        img = periodic_table_8k(oracle)
     src, dst = ctx.image_from_host(img), ctx.image_create(w, h, 1)
-    f = uniform(w, h, grayscale=1, blur=1, blur_radius=21, edge_detect=1)
-    s = ctx.chain(f, src, dst, nb.NORM_CS_RAW)[0]
-    got = dst.download()[0]
-    # (1) bands incl. top and bottom edges vs the oracle run on the band + its stencil halo
-    for y0, y1 in ((0, 96), (2100, 2196), (h - 96, h)):
-        lo, hi = max(0, y0 - 12), min(h, y1 + 12)
-        band = np.ascontiguousarray(img[lo:hi])
-        eo, _ = oracle.chain(band, oracle.make_uniform(w, hi - lo, grayscale=1, blur=1, blur_radius=21, edge_detect=1), oracle.CS_RAW)
-        assert np.array_equal(got[y0:y1], eo[y0 - lo:y1 - lo]), (y0, y1)
-    # (2) output structure: gray, opaque
-    assert (got[..., 3] == 255).all() and np.array_equal(got[..., 0], got[..., 1]) and np.array_equal(got[..., 0], got[..., 2])
-    # (3) SSIM of the chain output vs source equals the oracle's SSIM on the GPU output
-    assert abs(s - oracle.ssim(got, img)) <= SSIM_TIGHT
-    # (4) idempotent front stage; SSIM(x,x) == 1
+    for r in (3, 7, 21, 39):
+        f = uniform(w, h, grayscale=1, blur=1, blur_radius=r, edge_detect=1)
+        s = ctx.chain(f, src, dst, nb.NORM_CS_RAW)[0]
+        got = dst.download()[0]
+        # (1) bands incl. top and bottom edges vs the oracle run on the band + its stencil halo
+        halo = (r - 1) // 2 + 2
+        for y0, y1 in ((0, 64), (2100, 2164), (h - 64, h)):
+            lo, hi = max(0, y0 - halo), min(h, y1 + halo)
+            band = np.ascontiguousarray(img[lo:hi])
+            eo, _ = oracle.chain(band, oracle.make_uniform(w, hi - lo, grayscale=1, blur=1, blur_radius=r, edge_detect=1), oracle.CS_RAW)
+            assert np.array_equal(got[y0:y1], eo[y0 - lo:y1 - lo]), (content, r, y0, y1)
+        # (2) output structure: gray, opaque
+        assert (got[..., 3] == 255).all() and np.array_equal(got[..., 0], got[..., 1]) and np.array_equal(got[..., 0], got[..., 2])
+        # (3) SSIM of the chain output vs source equals the oracle's SSIM on the GPU output
+        assert abs(s - oracle.ssim(got, img)) <= SSIM_TIGHT, (content, r)
+    # (4) SSIM(x,x) == 1
     assert abs(ctx.ssim(src, src)[0] - 1.0) <= 1e-12
     src.destroy(), dst.destroy()
 
