@@ -1,6 +1,9 @@
 //! FFI to `libnorm_cuda.so` (C ABI: `include/norm_cuda.h`) and a safe wrapper with the shape of
 //! norm's own effect API: `FeatureUniform` in, decoded image in, RGBA8 buffer out.
-//! UNVERIFIED: written without a Rust toolchain; mirrors the header one-to-one.
+//! UNVERIFIED: written without a Rust toolchain.  The `extern "C"` blocks (`ffi.rs`) are GENERATED from
+//! `include/norm_cuda.h` and `include/norm_nccl.h` by `tools/gen_rust_ffi.py`: one declaration per exported symbol, and
+//! `tests/test_host.py` checks that list against `nm -D` of the built libraries.  The `#[repr(C)]` structs below are
+//! written by hand; their sizes are asserted at compile time against the sizes the C side asserts.
 #![allow(non_camel_case_types)]
 use std::ffi::{c_char, c_void, CStr};
 
@@ -8,6 +11,10 @@ pub type norm_status = i32;
 pub const NORM_OK: norm_status = 0;
 pub const NORM_CS_REFERENCE: u32 = 0;
 pub const NORM_CS_RAW: u32 = 1;
+pub const NORM_OUT_SRGB: u32 = 2;
+pub const NORM_LUMA_RGB: i32 = 0;
+pub const NORM_LUMA_GRAY: i32 = 1;
+pub const NORM_LUMA_GRAY_UNIT: i32 = 2;
 pub const NORM_EXPAND_COMPAT: i32 = 0;
 pub const NORM_EXPAND_SPEC: i32 = 1;
 
@@ -15,6 +22,10 @@ pub const NORM_EXPAND_SPEC: i32 = 1;
 pub struct norm_ctx { _p: [u8; 0] }
 #[repr(C)]
 pub struct norm_img { _p: [u8; 0] }
+#[repr(C)]
+pub struct norm_band { _p: [u8; 0] }
+#[repr(C)]
+pub struct norm_nccl_comm { _p: [u8; 0] }
 
 /// `FeatureUniform` of norm (src/renderer/feature_uniform.rs:1-17), 112 bytes.
 #[repr(C)]
@@ -51,6 +62,8 @@ pub struct NormPngDesc {
     pub n_trns: i32,
 }
 
+const _: () = assert!(std::mem::size_of::<NormPngDesc>() == 64);
+
 /// The inflated IDAT stream as `ScanlineReader::new` receives it (src/png/scanline_reader.rs:15-28).
 #[repr(C)]
 pub struct NormInflatedDesc {
@@ -63,6 +76,29 @@ pub struct NormInflatedDesc {
     pub data: *const u8,
     pub len: usize,
 }
+
+const _: () = assert!(std::mem::size_of::<NormInflatedDesc>() == 32);
+
+/// What one rank of a row-band sharded image tells the others (`norm_cuda_band_export`), 256 bytes.
+#[repr(C)]
+#[derive(Clone, Copy)]
+pub struct NormBandHandle {
+    pub mem: [u8; 64],
+    pub ready_event: [u8; 64],
+    pub halo_event: [u8; 64],
+    pub pitch: u64,
+    pub local_ptr: u64,
+    pub local_ready: u64,
+    pub local_halo: u64,
+    pub pid: u64,
+    pub row0: u32,
+    pub rows: u32,
+    pub halo_up: u32,
+    pub halo_down: u32,
+    pub rank: i32,
+    pub device: i32,
+}
+const _: () = assert!(std::mem::size_of::<NormBandHandle>() == 256);
 
 /// src/renderer/shape_uniform.rs:3-10
 #[repr(C)]
@@ -84,6 +120,8 @@ pub struct NormCircleData {
     pub _padding: f32,
 }
 
+const _: () = assert!(std::mem::size_of::<NormShapeUniform>() == 16 && std::mem::size_of::<NormCircleData>() == 16);
+
 /// src/renderer/draw_uniform.rs:3-9
 #[repr(C)]
 #[derive(Clone, Copy, Debug, Default)]
@@ -96,33 +134,8 @@ pub struct NormDrawUniform {
 }
 const _: () = assert!(std::mem::size_of::<NormDrawUniform>() == 80);
 
-extern "C" {
-    pub fn norm_cuda_abi_version() -> i32;
-    pub fn norm_cuda_create(device: i32, out: *mut *mut norm_ctx) -> norm_status;
-    pub fn norm_cuda_destroy(ctx: *mut norm_ctx);
-    pub fn norm_cuda_last_error(ctx: *const norm_ctx) -> *const c_char;
-    pub fn norm_cuda_sync(ctx: *mut norm_ctx) -> norm_status;
-    pub fn norm_cuda_image_create(ctx: *mut norm_ctx, w: u32, h: u32, frames: u32, out: *mut *mut norm_img) -> norm_status;
-    pub fn norm_cuda_image_destroy(ctx: *mut norm_ctx, img: *mut norm_img);
-    pub fn norm_cuda_upload(ctx: *mut norm_ctx, img: *mut norm_img, frame0: u32, n: u32, host: *const u8, pitch: usize) -> norm_status;
-    pub fn norm_cuda_download(ctx: *mut norm_ctx, img: *const norm_img, frame0: u32, n: u32, host: *mut u8, pitch: usize) -> norm_status;
-    pub fn norm_cuda_expand_rgba8(ctx: *mut norm_ctx, png: *const NormPngDesc, mode: i32, out: *mut norm_img, frame: u32) -> norm_status;
-    pub fn norm_cuda_effects(ctx: *mut norm_ctx, f: *const NormFeatureUniform, flags: u32, input: *const norm_img, out: *mut norm_img) -> norm_status;
-    pub fn norm_cuda_chain(ctx: *mut norm_ctx, f: *const NormFeatureUniform, flags: u32, input: *const norm_img, out: *mut norm_img, ssim: *mut f64) -> norm_status;
-    pub fn norm_cuda_chain_host(ctx: *mut norm_ctx, f: *const NormFeatureUniform, flags: u32, input: *const u8, out: *mut u8, frames: u32, ssim: *mut f64) -> norm_status;
-    pub fn norm_cuda_chain_band(ctx: *mut norm_ctx, f: *const NormFeatureUniform, flags: u32, input: *const norm_img, out: *mut norm_img, own_row0: u32, own_rows: u32, moments: *mut f64) -> norm_status;
-    pub fn norm_cuda_ssim(ctx: *mut norm_ctx, a: *const norm_img, b: *const norm_img, ssim: *mut f64) -> norm_status;
-    pub fn norm_cuda_ssim_moments(ctx: *mut norm_ctx, a: *const norm_img, b: *const norm_img, moments: *mut f64) -> norm_status;
-    pub fn norm_ssim_from_moments(moments: *const f64, npix: f64) -> f64;
-    pub fn norm_cuda_unfilter(ctx: *mut norm_ctx, inflated: *const NormInflatedDesc, pixel_buffer: *mut u8) -> norm_status;
-    pub fn norm_cuda_unfilter_expand_rgba8(ctx: *mut norm_ctx, inflated: *const NormInflatedDesc, plte: *const u8, n_plte: i32, trns: *const u8, n_trns: i32, mode: i32, out: *mut norm_img, frame: u32) -> norm_status;
-    pub fn norm_cuda_unfilter_expand_rgba8_batch(ctx: *mut norm_ctx, inflated: *const NormInflatedDesc, n: u32, plte: *const u8, n_plte: i32, trns: *const u8, n_trns: i32, mode: i32, out: *mut norm_img, frame0: u32) -> norm_status;
-    pub fn norm_cuda_filter_scanlines(ctx: *mut norm_ctx, width: u32, height: u32, bit_depth: u8, color_type: u8, pixel_buffer: *const u8, paeth_compat: i32, stream: *mut u8, filter_types: *mut u8) -> norm_status;
-    pub fn norm_cuda_filter_image(ctx: *mut norm_ctx, img: *const norm_img, frame: u32, paeth_compat: i32, stream: *mut u8, filter_types: *mut u8) -> norm_status;
-    pub fn norm_cuda_box_blur(ctx: *mut norm_ctx, input: *const norm_img, out: *mut norm_img) -> norm_status;
-    pub fn norm_cuda_overlay(ctx: *mut norm_ctx, shapes: *const NormShapeUniform, circles: *const NormCircleData, draw: *const NormDrawUniform, input: *const norm_img, out: *mut norm_img) -> norm_status;
-    pub fn norm_cuda_ssim_static(a: *const c_void, b: *const c_void, w: u32, h: u32, frames: u32, pitch: usize, frame_stride: usize, ssim_dev: *mut f64, moments_dev: *mut f64, stream: *mut c_void) -> norm_status;
-}
+mod ffi;
+pub use ffi::*;
 
 fn check(ctx: *const norm_ctx, status: norm_status) -> anyhow::Result<()> {
     if status == NORM_OK {

@@ -25,6 +25,27 @@ def test_library_exports_every_declared_symbol():
     assert nb.load().norm_cuda_abi_version() == 1
 
 
+def test_rust_sys_crate_declares_every_exported_symbol():
+    """rust/norm-cuda-sys/src/ffi.rs is generated from the headers (tools/gen_rust_ffi.py): it must be current, and
+    the symbols it declares must be exactly the norm_* functions the two libraries export (nm -D)."""
+    import subprocess
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import gen_rust_ffi
+    text, names = gen_rust_ffi.render()
+    assert open(gen_rust_ffi.OUT).read() == text, "run `python tools/gen_rust_ffi.py`"
+    exported = set()
+    for lib in (nb.LIB_PATH, os.path.join(os.path.dirname(nb.LIB_PATH), "libnorm_nccl.so")):
+        out = subprocess.run(["nm", "-D", "--defined-only", lib], capture_output=True, text=True, check=True).stdout
+        exported |= {ln.split()[-1] for ln in out.splitlines() if ln.split()[-2:-1] == ["T"] and ln.split()[-1].startswith("norm_")}
+    assert set(names) == exported, set(names) ^ exported
+    # the hand-written structs carry the sizes the C side asserts
+    rs = open(os.path.join(ROOT, "rust", "norm-cuda-sys", "src", "lib.rs")).read()
+    for name, size in (("NormFeatureUniform", 112), ("NormPngDesc", C.sizeof(nb._lib.NormPngDesc)), ("NormBandHandle", 256),
+                       ("NormInflatedDesc", C.sizeof(nb._lib.NormInflatedDesc)), ("NormDrawUniform", 80)):
+        assert re.search(r"size_of::<%s>\(\) == %d" % (name, size), rs), (name, size)
+
+
 def test_no_oracle_or_cpu_fallback_in_product():
     """The product must not reach into oracle/ (task rule 3)."""
     for dirpath, _, files in os.walk(os.path.join(ROOT, "norm_b200")):
