@@ -3,7 +3,7 @@
 // grayscale, invert) applied to the pixels as they are loaded, so a reference frame "compute chain ->
 // one fragment effect" is one pass over HBM (4 B read + 4 B written per pixel).
 //
-// One warp owns a tile of 120 x 18 output pixels; lane i loads columns x0-4+4i .. +3 (lanes 0 and 31 only
+// One warp owns a tile of 120 x 36 output pixels; lane i loads columns x0-4+4i .. +3 (lanes 0 and 31 only
 // feed their neighbours' halo) and marches down the rows with a window of 3 rows x (1 + 4 + 1) elements
 // in registers.  Per row a lane issues ONE 16-byte load, converts its four pixels once (Sobel: intensity)
 // and gets the two halo elements from its neighbours with warp shuffles: no divergence away from the
@@ -13,7 +13,7 @@
 
 namespace normk {
 
-constexpr int kS3Rows = 18;   // rows per warp tile
+constexpr int kS3Rows = 36;   // rows per warp tile (38 rows loaded: 5.5 % halo)
 constexpr int kS3Cols = 120;  // output columns per warp tile: lanes 1..30 x 4 pixels
 enum { kOpSobel = 0, kOpSharpen = 1, kOpBox = 2 };
 
@@ -36,7 +36,8 @@ __device__ __forceinline__ uint32_t s3_front(uint32_t p, const uint8_t *slut, ui
 }
 
 // window element: Sobel keeps the intensity, sharpen the pixel, the box blur the pixel split into its
-// even and odd bytes (two 16-bit lanes per word, so byte sums add up without carries between channels)
+// even and odd bytes (two 16-bit lanes per word, so byte sums add up without carries between channels) and
+// summed with its left and right neighbours
 template <int OP>
 struct S3Elem {
     uint32_t a, b;
@@ -47,8 +48,10 @@ struct S3Elem {
 // intensity (those are >= 1) and gives a magnitude that rounds to 0 when all nine are zero, so the
 // bytes written equal those of the exact 0 -- and the compare / select of the zero case is not needed.
 __device__ __forceinline__ float s3_intensity(uint32_t p) {
-    const float r = byte_f_alu(p, 0), g = byte_f_alu(p, 1), b = byte_f_alu(p, 2);  // ALU unpack: the conversion pipe is slower here
-    const float a = fmaxf(__fmaf_rn(b, b, __fmaf_rn(g, g, __fmul_rn(r, r))), 1e-30f);
+    // r^2 + g^2 + b^2 is an integer < 2^18: one four-way byte dot product of the pixel with itself (alpha masked) and
+    // one exact conversion give the same float as the three unpacks and three multiply-adds
+    const uint32_t rgb = p & 0x00ffffffu;
+    const float a = fmaxf((float)__dp4a(rgb, rgb, 0u), 1e-30f);
     float y;
     asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(a));
     float s = __fmul_rn(a, y);
@@ -107,12 +110,9 @@ __device__ __forceinline__ uint32_t s3_apply(const S3Elem<OP> (&top)[6], const S
         return pack_rgba((uint32_t)__vimin_s32_relu(v0, 255), (uint32_t)__vimin_s32_relu(v1, 255),
                          (uint32_t)__vimin_s32_relu(v2, 255), (uint32_t)__vimin_s32_relu(v3, 255));
     } else {
-        uint32_t se = 0, so = 0;
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            se += top[j + k].a + mid[j + k].a + bot[j + k].a;
-            so += top[j + k].b + mid[j + k].b + bot[j + k].b;
-        }
+        // window elements of the box blur are HORIZONTAL three-pixel sums (see convert): three adds per lane pair
+        const uint32_t se = top[j + 1].a + mid[j + 1].a + bot[j + 1].a;
+        const uint32_t so = top[j + 1].b + mid[j + 1].b + bot[j + 1].b;
         return pack_rgba(div9_round(se & 0xffffu), div9_round(so & 0xffffu), div9_round(se >> 16), div9_round(so >> 16));
     }
 }
@@ -136,10 +136,17 @@ __global__ void __launch_bounds__(256, 4) stencil3_kernel(ImgView in, ImgView ou
         const int x0 = (int)(tr % tiles_x) * kS3Cols, y0 = (int)(tr / tiles_x) * kS3Rows;
         // lanes 0 and 31 only feed their neighbours' halo: lane i loads columns x0 - 4 + 4i .. + 3
         const int col = x0 - 4 + 4 * lane;
-        const bool vec = col >= 0 && col + 3 < W;                     // one aligned 16-byte access
+        const bool vec = col >= 0 && col + 3 < W;                     // the whole 16-byte access lies inside the row
         const bool writes = lane >= 1 && lane <= 30 && col < W;
         const uint8_t *fbase = in.ptr + (size_t)f * in.frame_stride;
         const uint32_t ipitch = (uint32_t)in.pitch;
+        // Every lane loads ONE aligned 16-byte chunk: its own, or - for lanes left / right of the image - the first /
+        // last chunk of the row (rows are pitched to 16 bytes, so the chunk that holds pixel W-1 is readable to its
+        // end).  ClampToEdge is then a register fix-up that only tiles on the image border execute (tile-uniform
+        // branch); interior tiles pay one address computation and one load per row, nothing else.
+        const int colc = clampi(col, 0, ((W - 1) >> 2) << 2);
+        const bool border_tile = x0 == 0 || x0 + kS3Cols + 4 > W;
+        const uint8_t *lbase = fbase + (size_t)colc * 4;
 
         // fetch(r): this lane's 16 bytes of row r (ClampToEdge).  Fetches run two rows ahead of the arithmetic
         // so that every lane keeps two loads in flight.
@@ -147,23 +154,37 @@ __global__ void __launch_bounds__(256, 4) stencil3_kernel(ImgView in, ImgView ou
             uint32_t p[4];
         };
         auto fetch = [&](int r) {
-            const uint8_t *row = fbase + (uint64_t)(uint32_t)clampi(r, 0, H - 1) * ipitch;
+            const uint4 v = ldg_stream(reinterpret_cast<const uint4 *>(lbase + (uint64_t)(uint32_t)clampi(r, 0, H - 1) * ipitch));
             Raw q;
-            if (vec) {
-                const uint4 v = ldg_stream(reinterpret_cast<const uint4 *>(row + (size_t)col * 4));
-                q.p[0] = v.x, q.p[1] = v.y, q.p[2] = v.z, q.p[3] = v.w;
-            } else {  // tiles on the left / right image border
-                const uint32_t *rp = reinterpret_cast<const uint32_t *>(row);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) q.p[j] = rp[clampi(col + j, 0, W - 1)];
-            }
+            q.p[0] = v.x, q.p[1] = v.y, q.p[2] = v.z, q.p[3] = v.w;
             return q;
         };
-        auto convert = [&](const Raw &q, S3Elem<OP>(&w)[6]) {
+        auto convert = [&](const Raw &qin, S3Elem<OP>(&w)[6]) {
+            Raw q = qin;
+            // (ClampToEdge fix-up here, where the data is consumed, not in fetch: touching the registers there would
+            // make every load wait for its data at once and undo the two-rows-ahead prefetch)
+            if (border_tile && !vec) {
+                // element of the loaded chunk that holds the clamped pixel: column 0 left of the image, column W-1 otherwise
+                const int le = (W - 1) & 3;
+                const uint32_t last = le == 0 ? q.p[0] : le == 1 ? q.p[1] : le == 2 ? q.p[2] : q.p[3];
+                const uint32_t edge = col < 0 ? q.p[0] : last;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (col + j < 0 || col + j > W - 1) q.p[j] = edge;
+            }
 #pragma unroll
             for (int j = 0; j < 4; ++j) w[1 + j] = s3_conv<OP>(s3_front<FR>(q.p[j], slut, inv_mask));
             w[0] = s3_shfl_up<OP>(w[4]);
             w[5] = s3_shfl_down<OP>(w[1]);
+            if (OP == kOpBox) {
+                // the nine bytes of a channel sum exactly in integers whatever the order: keep, per row, the sum of each
+                // output column's three horizontal neighbours (two thirds of the window registers, fewer adds per pixel)
+                S3Elem<OP> h[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) h[j].a = w[j].a + w[j + 1].a + w[j + 2].a, h[j].b = w[j].b + w[j + 1].b + w[j + 2].b;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) w[1 + j] = h[j];
+            }
         };
 
         uint8_t *obase = out.ptr + (size_t)f * out.frame_stride;
@@ -174,12 +195,12 @@ __global__ void __launch_bounds__(256, 4) stencil3_kernel(ImgView in, ImgView ou
             convert(qa, wa);
             convert(qb, wb);
         }
-        Raw q0 = fetch(y0 + 1), q1 = fetch(y0 + 2);  // rows r+1 and r+2 of the row being computed
+        Raw q0 = fetch(y0 + 1), q1 = fetch(y0 + 2), q2 = fetch(y0 + 3);  // rows r+1 .. r+3 of the row being computed: three loads in flight
         // "top" is row r+1: texture v grows downward (image_shader.wgsl:136-146)
 #define S3_ROW(R_, BOT, MID, TOP, QCUR, QNEXT)                                                            \
     if ((R_) < H) {                                                                                       \
         convert(QCUR, TOP);                                                                               \
-        QCUR = fetch((R_) + 3);                                                                           \
+        QCUR = fetch((R_) + 4);                                                                           \
         uint32_t o[4];                                                                                    \
         _Pragma("unroll") for (int j = 0; j < 4; ++j) o[j] = s3_apply<OP>(TOP, MID, BOT, j, factor);      \
         uint8_t *orow = obase + (uint64_t)(uint32_t)(R_) * opitch;                                        \
@@ -192,16 +213,13 @@ __global__ void __launch_bounds__(256, 4) stencil3_kernel(ImgView in, ImgView ou
             }                                                                                             \
         }                                                                                                 \
     }
-        // 6 rows per trip: the window rotates with period 3, the fetch queue with period 2
-        static_assert(kS3Rows % 6 == 0, "row loop below is unrolled 6 x");
+        // 3 rows per trip: the window and the fetch queue both rotate with period 3
+        static_assert(kS3Rows % 3 == 0, "row loop below is unrolled 3 x");
 #pragma unroll 1
-        for (int r = y0; r < y0 + kS3Rows; r += 6) {
+        for (int r = y0; r < y0 + kS3Rows; r += 3) {
             S3_ROW(r, wa, wb, wc, q0, q1)
-            S3_ROW(r + 1, wb, wc, wa, q1, q0)
-            S3_ROW(r + 2, wc, wa, wb, q0, q1)
-            S3_ROW(r + 3, wa, wb, wc, q1, q0)
-            S3_ROW(r + 4, wb, wc, wa, q0, q1)
-            S3_ROW(r + 5, wc, wa, wb, q1, q0)
+            S3_ROW(r + 1, wb, wc, wa, q1, q2)
+            S3_ROW(r + 2, wc, wa, wb, q2, q0)
         }
 #undef S3_ROW
     }
