@@ -57,7 +57,26 @@ def build_cuda(force=False, verbose=False):
         sys.stderr.write(r.stdout + r.stderr)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed, see " + log)
+    check_spills(r.stdout + r.stderr)
     return LIB
+
+
+def check_spills(ptxas_log):
+    """The pipelined chain kernel (chain_fused2_kernel<R, GRAY, FRONT, MODE 0>: the headline path) must not spill:
+    its register budgets are tuned per warp group and a spill in a hot loop costs tens of percent.  ptxas -v reports
+    spills per entry function; any non-zero count for a MODE 0 instantiation fails the build."""
+    import re
+    bad, cur = [], None
+    for line in ptxas_log.splitlines():
+        m = re.search(r"Function properties for (\S+)", line)
+        if m:
+            cur = m.group(1)
+            continue
+        m = re.search(r"(\d+) bytes spill stores", line)
+        if m and cur and "chain_fused2_kernel" in cur and cur.endswith("ELi0EEEvNS_11FusedParamsE") and int(m.group(1)) > 0:
+            bad.append((cur, int(m.group(1))))
+    if bad:
+        raise RuntimeError("register spills in the pipelined chain kernel: " + ", ".join(f"{n} ({b} B)" for n, b in bad))
 
 
 NCCL_LIB = os.path.join(ROOT, "norm_b200", "libnorm_nccl.so")

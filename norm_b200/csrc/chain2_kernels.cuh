@@ -88,6 +88,7 @@ struct Fused2Cfg {
     // register budgets (setmaxnreg), summing to 3 x 80
     static constexpr int REGS_H = MODE == 1 ? (GRAY ? 56 : NORM_C2_REGS_H4) : NORM_C2_REGS_A;              // MODE 1 + GRAY: two H groups
     static constexpr int REGS_V = MODE == 1 ? (GRAY ? 128 : (240 - NORM_C2_REGS_H4) / 2) : NORM_C2_REGS_B;
+    static constexpr int REGS_C = MODE == 0 ? 240 - REGS_H - REGS_V : 0;
     // source byte of channel c: MODE 1 + GRAY blurs (y, alpha) = bytes (0, 3)
     __host__ __device__ static constexpr int chan_byte(int c) { return (MODE == 1 && GRAY && c == 1) ? 3 : c; }
     static constexpr int IS = 128;                      // intensity row stride
@@ -434,7 +435,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
             blur_only_consumer<C, R, GRAY, 0, 2, kABParties>(p, Hb_base, tid - kC2Group, items_per_frame, total);
             return;
         }
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(NORM_C2_REGS_B));
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REGS_V));
         const int bcol = tid - kC2Group;  // blurred column of the strip owned by this thread
         const bool active = bcol < C::BW;
 
@@ -530,7 +531,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
             blur_only_consumer<C, R, GRAY, 2, 2, kABParties>(p, Hb_base, tid - 2 * kC2Group, items_per_frame, total);
             return;
         }
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(NORM_C2_REGS_C));
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(C::REGS_C));
 #if NORM_C2_CPAIR
         // Pair version.  A thread owns TWO adjacent output columns (one 8-byte store, one 8-byte source load per row);
         // warps 0/1 of the group take the column halves of batch rows [0, JH), warps 2/3 those of rows [JH, RB), so all

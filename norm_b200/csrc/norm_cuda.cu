@@ -547,12 +547,20 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
     return NORM_OK;
 }
 
+#ifndef NORM_GEN2_RGB_MAX_R
+#define NORM_GEN2_RGB_MAX_R 23   // chain on RGB: group B keeps 3 x R running outputs in registers and R + 1 tap pairs in
+                                 // the 63 uniform registers; from r = 25 on the pairs no longer fit and the kernel spills
+#endif
+#ifndef NORM_GEN2_RGBA_MAX_R
+#define NORM_GEN2_RGBA_MAX_R 27  // blur of four channels: groups B and C keep 2 x R running outputs each (spills from r = 29)
+#endif
+
 template <int R>
 norm_status launch_fused_r(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
                            double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1) {
-    // second-generation kernel (column-owner consumer) where its register budget allows: R <= 21
-    // (group B keeps CH*R running outputs in registers: any radius on one channel, R <= 21 on RGB)
-    if constexpr (R <= 21) {
+    // second-generation kernel (column-owner consumer) where its register budget allows
+    // (group B keeps CH*R running outputs in registers: any radius on one channel, R <= 23 on RGB)
+    if constexpr (R <= NORM_GEN2_RGB_MAX_R) {
         if (ctx->fused_gen != 1) {
             if (p.gray) return launch_fused<R, true, true, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
             if (p.front) return launch_fused<R, false, true, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
@@ -573,7 +581,7 @@ template <int R>
 norm_status launch_fused_rx(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
                             double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1, bool *fused) {
     if (p.gray) return launch_fused<R, true, true, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
-    if constexpr (R <= 21) {
+    if constexpr (R <= NORM_GEN2_RGB_MAX_R) {
         if (ctx->fused_gen == 1) {
             *fused = false;
             return NORM_OK;
@@ -599,7 +607,7 @@ norm_status launch_blur_only_r(norm_ctx *ctx, Slot &slot, const StagePlan &p, co
                                bool *fused) {
     *fused = true;
     if (p.gray) return launch_fused<R, true, true, 3>(ctx, slot, p, in, out, nullptr, nullptr, 0, in.h);
-    if constexpr (R <= 21) {
+    if constexpr (R <= NORM_GEN2_RGBA_MAX_R) {
         if (p.front) return launch_fused<R, false, true, 3>(ctx, slot, p, in, out, nullptr, nullptr, 0, in.h);
         return launch_fused<R, false, false, 3>(ctx, slot, p, in, out, nullptr, nullptr, 0, in.h);
     }
