@@ -57,7 +57,8 @@ def build_cuda(force=False, verbose=False):
         sys.stderr.write(r.stdout + r.stderr)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed, see " + log)
-    check_spills(r.stdout + r.stderr)
+    if not os.environ.get("NORM_ALLOW_SPILLS"):  # (experiments with other register budgets set it)
+        check_spills(r.stdout + r.stderr)
     return LIB
 
 

@@ -497,20 +497,22 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                             }
                             // round-half-even through the 1.5*2^23 trick; after grayscale only the byte (the low
                             // mantissa bits of the biased sum) is needed, so the subtraction is skipped
-                            v[c] = GRAY ? __fadd_rn(o, 12582912.0f) : round_rne(o);
+                            // the quantised byte sits in the low mantissa bits of (o + 1.5*2^23)
+                            v[c] = __fadd_rn(o, 12582912.0f);
                         }
                         {
                             float I;
-                            if (GRAY)
+                            if (GRAY) {
                                 I = intLut[__float_as_uint(v[0]) & 0xffu];
-                            else
-#if NORM_C2_SQRT_NOSEL
-                                I = sqrt_rn_inrange0(__fmaf_rn(v[C::CH - 1], v[C::CH - 1],
-                                                              __fmaf_rn(v[C::CH > 1 ? 1 : 0], v[C::CH > 1 ? 1 : 0], __fmul_rn(v[0], v[0]))));
-#else
-                                I = sqrt_rn_inrange(__fmaf_rn(v[C::CH - 1], v[C::CH - 1],
-                                                              __fmaf_rn(v[C::CH > 1 ? 1 : 0], v[C::CH > 1 ? 1 : 0], __fmul_rn(v[0], v[0]))));
-#endif
+                            } else {
+                                // r^2 + g^2 + b^2 of the three quantised bytes: pack them (two PRMT) and take one byte dot
+                                // product; the radicand is an integer < 2^18, so its conversion is exact and equals the
+                                // float sum of squares the oracle forms
+                                const uint32_t rg = __byte_perm(__float_as_uint(v[0]), __float_as_uint(v[C::CH > 1 ? 1 : 0]), 0x7740);
+                                // (byte 1 of the biased float's bits 0x4B4000qq is zero: it fills the fourth lane)
+                                const uint32_t rgb = __byte_perm(rg, __float_as_uint(v[C::CH - 1]), 0x5410);
+                                I = sqrt_rn_inrange0((float)__dp4a(rgb, rgb, 0u));
+                            }
                             ist[j * C::IS] = I;
 #if NORM_C2_CPAIR
                             if (j == C::RB - 2) icarry0 = I;
