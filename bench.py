@@ -280,12 +280,16 @@ def main():
             sampler.start()
             time.sleep(0.3)
         l0, t0 = ctx.launch_count(), time.time()
+        if sample_clocks:  # `ncu --profile-from-start off` then lists exactly the timed region's launches
+            torch.cuda.cudart().cudaProfilerStart()
         ctx.timer_start()
         for _ in range(steps):
             ctx.chain_async(f, src, dst, nb.NORM_CS_RAW, ssim_t.data_ptr())
         ctx.timer_stop()
         ms = ctx.timer_elapsed_ms()
         ctx.sync()
+        if sample_clocks:
+            torch.cuda.cudart().cudaProfilerStop()
         t1 = time.time()
         barrier()
         clocks = sampler.stop(t0, t1) if sampler else None
