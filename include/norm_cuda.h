@@ -250,7 +250,10 @@ norm_status norm_cuda_effects(norm_ctx *ctx, const NormFeatureUniform *f, uint32
 norm_status norm_cuda_chain(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags,
                             const norm_img *in, norm_img *out, double *ssim);
 /* As norm_cuda_chain but returns without waiting; ssim_dev (device array of `frames` doubles,
- * may be NULL) receives the SSIM values on the context's stream. */
+ * may be NULL) receives the SSIM values on the context's stream.
+ * All `_async` entry points: scratch of the context (SSIM partial sums, stage temporaries) grows on demand, so the
+ * first call with a batch larger than any before it may call cudaMalloc and synchronise the device; later calls of
+ * that size or smaller allocate nothing. */
 norm_status norm_cuda_chain_async(norm_ctx *ctx, const NormFeatureUniform *f, uint32_t flags,
                                   const norm_img *in, norm_img *out, double *ssim_dev);
 
