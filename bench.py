@@ -397,7 +397,7 @@ def main():
         sys.path.insert(0, os.path.join(ROOT, "tools"))
         from band_run import band_benchmark
         band = band_benchmark(torch, dist, ctx, local_rank, rank, world, args.band_size, args.band_size, args.radius,
-                              steps=max(3, min(args.steps, 10)), warmup=2, verify="full")
+                              steps=20, warmup=3, verify="full")  # 20 steps queued back to back, one sync at the end
         band["config"] = "BASELINE.json configs[4]"
 
     cpu = None

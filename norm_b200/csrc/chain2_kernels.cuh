@@ -181,7 +181,12 @@ __device__ __forceinline__ void blur_only_consumer(const FusedParams &p, const f
         const uint32_t f = (uint32_t)(item / items_per_frame);
         const uint32_t irem = (uint32_t)(item - (size_t)f * items_per_frame);
         const int band = (int)(irem / p.strips), strip = (int)(irem - (uint32_t)band * p.strips);
-        const int x0 = strip * C::SW;
+        // The last strip of a row is shifted left so that it ends at the image's right edge (to a multiple of four columns:
+        // the staging copies are 16-byte aligned).  A ragged strip with a few valid columns would stage and blur 120
+        // columns through the slow clamped path and, with one item per CTA, set the kernel's time.  The `skip` columns the
+        // shifted strip shares with its neighbour are computed twice and stored once.
+        const int x0 = (W >= C::SW && strip * C::SW + C::SW > W) ? ((W - C::SW + 3) & ~3) : strip * C::SW;
+        const int skip = strip * C::SW - x0;
         const int ya = (int)p.out_y0 + band * (int)p.band_rows, yb = min(ya + (int)p.band_rows, (int)p.out_y1);
         const int NB = yb - ya;  // MODE 1: blurred rows == output rows
         const int nbatch = (NB + R - 1 + C::RB - 1) / C::RB;
@@ -199,7 +204,7 @@ __device__ __forceinline__ void blur_only_consumer(const FusedParams &p, const f
             const int slot = (int)(g & 1u);
             bar_sync(kB2Full0 + slot, kParties);
             if (active)
-                v_pass_batch<C, R, GRAY, C0, NCH>(p, Hb_base + slot * kHbFloats + bcol, b, NB, bx < W, orow, vacc2, vaccl);
+                v_pass_batch<C, R, GRAY, C0, NCH>(p, Hb_base + slot * kHbFloats + bcol, b, NB, bx < W && bcol >= skip, orow, vacc2, vaccl);
             __threadfence_block();
             bar_arrive(kB2Empty0 + slot, kParties);
         }
@@ -248,13 +253,15 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
     const uint32_t f = (uint32_t)(item / items_per_frame);                                              \
     const uint32_t irem = (uint32_t)(item - (size_t)f * items_per_frame);                               \
     const int band = (int)(irem / p.strips), strip = (int)(irem - (uint32_t)band * p.strips);           \
-    const int x0 = strip * C::SW;                                                                       \
+    /* last strip shifted left to end at the right image edge; its first `skip` columns belong to its neighbour */ \
+    const int x0 = (W >= C::SW && strip * C::SW + C::SW > W) ? ((W - C::SW + 3) & ~3) : strip * C::SW;               \
+    const int skip = strip * C::SW - x0;                                                                \
     const int ya = (int)p.out_y0 + band * (int)p.band_rows, yb = min(ya + (int)p.band_rows, (int)p.out_y1);                      \
     const int o_lo = max(ya - C::HALO, 0), o_hi = min(yb - 1 + C::HALO, Himg - 1); /* blurred rows needed */ \
     const int NB = o_hi - o_lo + 1;                                                                     \
     const int Q = NB + R - 1; /* rows of the clamped source sequence s(q) = clamp(o_lo - M + q) */      \
     const int nbatch = (Q + C::RB - 1) / C::RB;                                                         \
-    (void)x0, (void)NB
+    (void)x0, (void)NB, (void)skip
 
     // =========================== group A (and C in MODE 1): staging + H pass ===========================
     // ROLE 0 = group A: channels [0, CH_A).  ROLE 1 = group C in MODE 1 after grayscale: the alpha channel.
@@ -556,7 +563,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
             C2_ITEM_GEOMETRY();
             const int x = x0 + 2 * cpa;                   // first column of the pair
-            const bool full_strip = x0 + C::SW <= W;      // every pair of the strip lies inside the image
+            const bool full_strip = x0 + C::SW <= W && skip == 0;  // every pair of the strip lies inside the image and is this strip's own
             // intensity columns (index = blurred column + 1): the pair at ic, ic + 1; ClampToEdge on the blurred image
             const int ic = 2 * cpa + 2;
             const int il = (x - 1 < 0) ? ic : ic - 1;
@@ -681,7 +688,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
 #pragma unroll
                             for (int h = 0; h < 2; ++h) {
                                 const int xx = x + h;
-                                if (!act || xx >= W) continue;
+                                if (!act || xx >= W || 2 * cpa + h < skip) continue;
                                 const int c0 = ic + h;
                                 const int cl = (xx - 1 < 0) ? c0 : c0 - 1, cr = (xx + 1 > W - 1) ? c0 : c0 + 1;
                                 const uint32_t cb = sobel_mag_bits(rt[cl], rt[c0], rt[cr], rm[cl], rm[cr], rb[cl], rb[c0], rb[cr]);
@@ -718,7 +725,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
             C2_ITEM_GEOMETRY();
             const int x = x0 + tc;
-            const bool writes = tc < C::SW && x < W;
+            const bool writes = tc < C::SW && x < W && tc >= skip;
             const int xl = min(x, W - 1);  // keeps addresses valid on idle lanes
             // intensity column of x is tc+1; ClampToEdge: column -1 reads column 0, column W reads column W-1
             const int il = (x - 1 < 0) ? tc + 1 : tc, ic = min(tc + 1, C::IS - 1), ir = (x + 1 > W - 1) ? ic : min(tc + 2, C::IS - 1);
