@@ -43,6 +43,13 @@ def band_benchmark(torch, dist, ctx, local_rank, rank, world, height, width, rad
         dist.all_gather_object(out, obj, group=group)
         return out
 
+    def barrier():
+        # with the NCCL backend dist.barrier() only queues a kernel: wait for it, or the ranks enter the timed loop
+        # skewed and the wall clock of the early ones contains the wait for the late ones
+        torch.cuda.synchronize()
+        dist.barrier(group=group)
+        torch.cuda.synchronize()
+
     comm = None
     if use_nccl and world > 1:
         uid = [nccl.unique_id() if rank == 0 else None]
@@ -61,12 +68,12 @@ def band_benchmark(torch, dist, ctx, local_rank, rank, world, height, width, rad
         del t
     job.publish()
     ctx.sync()
-    dist.barrier(group=group)  # every rank has published its rows
+    barrier()  # every rank has published its rows
 
     for _ in range(max(warmup, 1)):
         job.step(nb.NORM_CS_RAW)
     job.sync()
-    dist.barrier(group=group)
+    barrier()
     t0 = time.perf_counter()
     ctx.timer_start()
     for _ in range(steps):
@@ -87,7 +94,7 @@ def band_benchmark(torch, dist, ctx, local_rank, rank, world, height, width, rad
         for _ in range(5):
             comm.allreduce_device(job.mom[0].device_ptr, 5, stream)
         job.sync()
-        dist.barrier(group=group)
+        barrier()
         t1 = time.perf_counter()
         for _ in range(100):
             comm.allreduce_device(job.mom[0].device_ptr, 5, stream)
@@ -131,6 +138,8 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--verify", default="seams", choices=["full", "seams", "none"])
+    ap.add_argument("--height", type=int, default=0)
+    ap.add_argument("--no-nccl", action="store_true", help="skip the all-reduce (timing experiments)")
     a = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -143,7 +152,8 @@ def main():
     os.environ.setdefault("MASTER_PORT", "29533")
     dist.init_process_group("gloo", rank=rank, world_size=world)
     ctx = nb.Context(local)
-    res = band_benchmark(torch, dist, ctx, local, rank, world, a.size, a.width or a.size, a.radius, a.steps, a.warmup, a.verify)
+    res = band_benchmark(torch, dist, ctx, local, rank, world, a.height or a.size, a.width or a.size, a.radius, a.steps, a.warmup, a.verify,
+                         use_nccl=not a.no_nccl)
     if rank == 0:
         print(json.dumps(res))
     ctx.close()
