@@ -118,6 +118,31 @@ __device__ __forceinline__ void st_global_pred_u16(void *ptr, uint32_t v, bool p
     asm volatile("{ .reg .pred p; setp.ne.u32 p, %0, 0; @p st.global.u16 [%1], %2; }" ::"r"((uint32_t)pred), "l"(ptr), "h"((uint16_t)v) : "memory");
 }
 
+// Which frame, strip and output rows [ya, yb) work item `item` stands for.  Static partition: item = (frame, band,
+// strip), bands of band_rows rows.  Balanced partition (one giant frame): CTA k = item % gridDim.x owns strip-rows
+// [k*per, (k+1)*per) of the strips laid end to end; its j-th item (j = item / gridDim.x) is the part of that range inside
+// strip (first strip + j); parts that do not exist are `empty` (every warp group skips them alike).
+__device__ __forceinline__ void c2_item_rows(const FusedParams &p, size_t item, uint32_t items_per_frame, uint32_t &f, int &strip,
+                                             int &ya, int &yb, bool &empty) {
+    if (p.balanced) {
+        const uint32_t rows = p.out_y1 - p.out_y0, k = (uint32_t)(item % gridDim.x), j = (uint32_t)(item / gridDim.x);
+        const uint32_t total = p.strips * rows, beg = k * p.per, end = min(total, beg + p.per);
+        const uint32_t col = beg / rows + j;
+        const uint32_t start = j == 0 ? beg : col * rows, stop = min(end, (col + 1) * rows);
+        f = 0, strip = (int)col;
+        empty = start >= stop || beg >= total;
+        ya = (int)(p.out_y0 + (empty ? 0u : start - col * rows));
+        yb = (int)(p.out_y0 + (empty ? 0u : stop - col * rows));
+    } else {
+        f = (uint32_t)(item / items_per_frame);
+        const uint32_t irem = (uint32_t)(item - (size_t)f * items_per_frame);
+        const int band = (int)(irem / p.strips);
+        strip = (int)(irem - (uint32_t)band * p.strips);
+        ya = (int)p.out_y0 + band * (int)p.band_rows, yb = min(ya + (int)p.band_rows, (int)p.out_y1);
+        empty = false;
+    }
+}
+
 // V pass of one batch for channels [C0, C0+NCH) of one blurred column (MODE 1): NCH x R running outputs in
 // registers (static rotation: the row loop is fully unrolled and RB % R == 0), quantise, store those bytes
 // of the RGBA8 result.  hp = H planes of this batch's slot at this thread's column.
@@ -178,16 +203,17 @@ __device__ __forceinline__ void blur_only_consumer(const FusedParams &p, const f
     bar_arrive(kB2Empty0, kParties);  // both H-plane slots start out empty
     bar_arrive(kB2Empty1, kParties);
     for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
-        const uint32_t f = (uint32_t)(item / items_per_frame);
-        const uint32_t irem = (uint32_t)(item - (size_t)f * items_per_frame);
-        const int band = (int)(irem / p.strips), strip = (int)(irem - (uint32_t)band * p.strips);
+        uint32_t f;
+        int strip, ya, yb;
+        bool empty = false;
+        c2_item_rows(p, item, items_per_frame, f, strip, ya, yb, empty);
+        if (empty) continue;
         // The last strip of a row is shifted left so that it ends at the image's right edge (to a multiple of four columns:
         // the staging copies are 16-byte aligned).  A ragged strip with a few valid columns would stage and blur 120
         // columns through the slow clamped path and, with one item per CTA, set the kernel's time.  The `skip` columns the
         // shifted strip shares with its neighbour are computed twice and stored once.
         const int x0 = (W >= C::SW && strip * C::SW + C::SW > W) ? ((W - C::SW + 3) & ~3) : strip * C::SW;
         const int skip = strip * C::SW - x0;
-        const int ya = (int)p.out_y0 + band * (int)p.band_rows, yb = min(ya + (int)p.band_rows, (int)p.out_y1);
         const int NB = yb - ya;  // MODE 1: blurred rows == output rows
         const int nbatch = (NB + R - 1 + C::RB - 1) / C::RB;
         const int bx = x0 + bcol;
@@ -243,25 +269,25 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
     __syncthreads();
 
     const uint32_t items_per_frame = p.strips * p.bands;
-    const size_t total = (size_t)items_per_frame * p.in.frames;
+    const size_t total = p.balanced ? (size_t)gridDim.x * p.maxi : (size_t)items_per_frame * p.in.frames;
     uint32_t g = 0;  // running batch counter: buffer slot = g & 1, identical sequence in all groups
     // threads meeting at the H-plane barriers: A + B, plus C when it shares the blur-only V pass (RGBA)
     constexpr int kABParties = (C::HGROUPS + C::VGROUPS) * kC2Group;  // producing + consuming groups
 
 // per-item geometry, identical in the three groups
 #define C2_ITEM_GEOMETRY()                                                                              \
-    const uint32_t f = (uint32_t)(item / items_per_frame);                                              \
-    const uint32_t irem = (uint32_t)(item - (size_t)f * items_per_frame);                               \
-    const int band = (int)(irem / p.strips), strip = (int)(irem - (uint32_t)band * p.strips);           \
+    uint32_t f;                                                                                         \
+    int strip, ya, yb;                                                                                  \
+    bool c2_empty = false;                                                                              \
+    c2_item_rows(p, item, items_per_frame, f, strip, ya, yb, c2_empty);                                 \
     /* last strip shifted left to end at the right image edge; its first `skip` columns belong to its neighbour */ \
     const int x0 = (W >= C::SW && strip * C::SW + C::SW > W) ? ((W - C::SW + 3) & ~3) : strip * C::SW;               \
     const int skip = strip * C::SW - x0;                                                                \
-    const int ya = (int)p.out_y0 + band * (int)p.band_rows, yb = min(ya + (int)p.band_rows, (int)p.out_y1);                      \
     const int o_lo = max(ya - C::HALO, 0), o_hi = min(yb - 1 + C::HALO, Himg - 1); /* blurred rows needed */ \
     const int NB = o_hi - o_lo + 1;                                                                     \
     const int Q = NB + R - 1; /* rows of the clamped source sequence s(q) = clamp(o_lo - M + q) */      \
     const int nbatch = (Q + C::RB - 1) / C::RB;                                                         \
-    (void)x0, (void)NB, (void)skip
+    (void)x0, (void)NB, (void)skip, (void)c2_empty
 
     // =========================== group A (and C in MODE 1): staging + H pass ===========================
     // ROLE 0 = group A: channels [0, CH_A).  ROLE 1 = group C in MODE 1 after grayscale: the alpha channel.
@@ -278,6 +304,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
 
         for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
             C2_ITEM_GEOMETRY();
+            if (c2_empty) continue;  // (balanced partition: this CTA's range ended in an earlier strip)
             const uint8_t *in_frame = p.in.ptr + (size_t)f * p.in.frame_stride;
             const uint32_t pitch32 = (uint32_t)p.in.pitch;
             // cp.async one batch of source rows (ClampToEdge in x and y) into staging buffer `buf`.
@@ -451,6 +478,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
 
         for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
             C2_ITEM_GEOMETRY();
+            if (c2_empty) continue;  // (balanced partition: this CTA's range ended in an earlier strip)
             float2 vacc2[C::CH][R / 2];  // running outputs: slots (2i, 2i+1) packed, slot R-1 alone
             float vaccl[C::CH];
 #if NORM_C2_CPAIR
@@ -562,6 +590,10 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
 
         for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
             C2_ITEM_GEOMETRY();
+            if (c2_empty) {  // (balanced partition) nothing to do: the finalize pass still sums this slot
+                if (p.do_ssim && tc < 5) p.partials[item * 5 + tc] = 0.0;
+                continue;
+            }
             const int x = x0 + 2 * cpa;                   // first column of the pair
             const bool full_strip = x0 + C::SW <= W && skip == 0;  // every pair of the strip lies inside the image and is this strip's own
             // intensity columns (index = blurred column + 1): the pair at ic, ic + 1; ClampToEdge on the blurred image
@@ -724,6 +756,10 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
 
         for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
             C2_ITEM_GEOMETRY();
+            if (c2_empty) {  // (balanced partition) nothing to do: the finalize pass still sums this slot
+                if (p.do_ssim && tc < 5) p.partials[item * 5 + tc] = 0.0;
+                continue;
+            }
             const int x = x0 + tc;
             const bool writes = tc < C::SW && x < W && tc >= skip;
             const int xl = min(x, W - 1);  // keeps addresses valid on idle lanes

@@ -80,6 +80,7 @@ struct norm_ctx {
     DevBuf results;     // per-frame moments (5) + ssim (1), doubles
     double *h_results = nullptr;
     size_t h_results_cap = 0;
+    int balanced_partition = 1;  // NORM_CUDA_BALANCED=0: static (band, strip) items only; 2: balanced ranges whenever possible (tests)
     uint32_t force_bands = 0;    // NORM_CUDA_BANDS: row bands per frame of the fused kernels (experiments)
     size_t chunk_bytes = 0;      // NORM_CUDA_CHUNK_BYTES: frames per chunk of the staged paths (tests: many small chunks)
     int fused_gen = 0;           // NORM_CUDA_FUSED_GEN=1 forces the first-generation fused kernel
@@ -529,15 +530,34 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
     if (ctx->force_bands) bands = std::min<uint32_t>(ctx->force_bands, out_rows);
     fp.band_rows = (out_rows + bands - 1) / bands;
     fp.bands = (out_rows + fp.band_rows - 1) / fp.band_rows;
+    // One giant frame (pipelined kernel): when the strips do not fill the last round, cut the strips' rows, laid end
+    // to end, into one contiguous range per CTA instead (a range that crosses a strip boundary costs one more pipeline
+    // fill).  274 strips of 4118 rows on 296 CTAs: 4148 row-equivalents per CTA become 3872.
+    size_t grid_items = (size_t)fp.strips * fp.bands * in.frames;
+    if (GEN != 1 && in.frames == 1 && !ctx->force_bands && ctx->balanced_partition) {
+        const uint64_t fill = (uint64_t)(R - 1) + C::RB / 2;
+        const uint64_t total_rows = (uint64_t)fp.strips * out_rows;
+        const uint64_t rounds = ((uint64_t)fp.strips * fp.bands + slots - 1) / slots;
+        const uint64_t cost_static = rounds * (fp.band_rows + fill);
+        const uint64_t per = std::max<uint64_t>(ctx->balanced_partition == 2 ? 7 : 64, (total_rows + slots - 1) / slots);
+        const uint64_t pieces = (per + out_rows - 1) / out_rows + 1;  // items a range can be cut into
+        const uint64_t cost_bal = per + std::min<uint64_t>(pieces, 2) * fill;
+        if ((cost_bal < cost_static || ctx->balanced_partition == 2) && total_rows < (1ull << 31)) {
+            fp.balanced = 1, fp.per = (uint32_t)per, fp.maxi = (uint32_t)pieces;
+            fp.bands = 1, fp.band_rows = out_rows;
+            grid_items = (size_t)((total_rows + per - 1) / per);
+        }
+    }
     fp.invert = p.inv ? 1u : 0u;
     fp.do_ssim = (d_ssim || d_moments) ? 1u : 0u;
     fp.ssim_y0 = std::max(y0, fp.out_y0), fp.ssim_y1 = std::max(fp.ssim_y0, std::min(y1, fp.out_y1));
-    const uint32_t items_per_frame = fp.strips * fp.bands;
+    const unsigned grid = grid_for(ctx, grid_items, per_sm);
+    // partial-sum slots per frame: one per work item (balanced: maxi per CTA, unused ones are written as zero)
+    const uint32_t items_per_frame = fp.balanced ? grid * fp.maxi : fp.strips * fp.bands;
     if (fp.do_ssim) {
         NORM_TRY(ensure_buf(ctx, slot.partials, (size_t)in.frames * items_per_frame * 5 * sizeof(double)));
         fp.partials = static_cast<double *>(slot.partials.p);
     }
-    const unsigned grid = grid_for(ctx, (size_t)items_per_frame * in.frames, per_sm);
     kern<<<grid, kThreads, C::kSmem, slot.stream>>>(fp);
     LAUNCH_CHECK(ctx);
     if (fp.do_ssim) {
@@ -754,6 +774,7 @@ norm_status create_impl(int32_t device, void *ext_stream, bool use_ext, norm_ctx
     ctx->device = device;
     if (const char *e = std::getenv("NORM_CUDA_FORCE_UNFUSED")) ctx->force_unfused = e[0] == '1';
     if (const char *e = std::getenv("NORM_CUDA_FUSED_GEN")) ctx->fused_gen = std::atoi(e);
+    if (const char *e = std::getenv("NORM_CUDA_BALANCED")) ctx->balanced_partition = std::atoi(e);
     if (const char *e = std::getenv("NORM_CUDA_BANDS")) ctx->force_bands = (uint32_t)std::atoi(e);
     if (const char *e = std::getenv("NORM_CUDA_CHUNK_BYTES")) ctx->chunk_bytes = (size_t)std::strtoull(e, nullptr, 10);
     auto bail = [&](cudaError_t ce, const char *what) {

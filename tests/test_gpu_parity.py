@@ -387,6 +387,25 @@ def test_chain_host_pipeline(ctx, oracle):
     ctx.host_free(ph), ctx.host_free(poh)
 
 
+def test_balanced_partition_of_one_frame(oracle, monkeypatch):
+    """One giant frame is cut into one contiguous range of strip-rows per CTA (items that start and end anywhere in a
+    strip, empty items, SSIM slots written as zero).  NORM_CUDA_BALANCED=2 forces that partition with ranges as short
+    as 7 rows, so small images exercise every case; results must equal the oracle and the static partition."""
+    monkeypatch.setenv("NORM_CUDA_BALANCED", "2")
+    with nb.Context(0) as c:
+        for (w, h) in [(1, 1), (5, 7), (130, 70), (333, 200), (1000, 517)]:
+            img = smooth_rgba(w, h, seed=w + h)
+            for kw in (dict(blur=1, blur_radius=21, edge_detect=1), dict(grayscale=1, blur=1, blur_radius=7, edge_detect=1),
+                       dict(blur=1, blur_radius=3, edge_detect=1), dict(blur=1, blur_radius=21), dict(grayscale=1, blur=1, blur_radius=21)):
+                f = uniform(w, h, **kw)
+                src, dst = c.image_from_host(img[None]), c.image_create(w, h, 1)
+                s = c.chain(f, src, dst, nb.NORM_CS_RAW)
+                eo, es = oracle.chain(img, oracle_uniform(oracle, f), oracle.CS_RAW)
+                assert np.array_equal(dst.download()[0], eo), (w, h, kw)
+                assert abs(s[0] - es) <= SSIM_TIGHT or (w * h == 1), (w, h, kw)
+                src.destroy(), dst.destroy()
+
+
 def test_multi_chunk_paths_bit_exact(oracle, monkeypatch):
     """The chunk loops only large batches reach: the host pipeline's slot reuse (chunk index mod 3) and the unfused
     chain's ping-pong temporaries rotating across chunks.  NORM_CUDA_CHUNK_BYTES (read when a context is created)
