@@ -122,10 +122,10 @@ __device__ __forceinline__ void st_global_pred_u16(void *ptr, uint32_t v, bool p
 // strip), bands of band_rows rows.  Balanced partition (one giant frame): CTA k = item % gridDim.x owns strip-rows
 // [k*per, (k+1)*per) of the strips laid end to end; its j-th item (j = item / gridDim.x) is the part of that range inside
 // strip (first strip + j); parts that do not exist are `empty` (every warp group skips them alike).
-__device__ __forceinline__ void c2_item_rows(const FusedParams &p, size_t item, uint32_t items_per_frame, uint32_t &f, int &strip,
+__device__ __forceinline__ void c2_item_rows(const FusedParams &p, uint32_t item, uint32_t items_per_frame, uint32_t &f, int &strip,
                                              int &ya, int &yb, bool &empty) {
     if (p.balanced) {
-        const uint32_t rows = p.out_y1 - p.out_y0, k = (uint32_t)(item % gridDim.x), j = (uint32_t)(item / gridDim.x);
+        const uint32_t rows = p.out_y1 - p.out_y0, k = item % gridDim.x, j = item / gridDim.x;
         const uint32_t total = p.strips * rows, beg = k * p.per, end = min(total, beg + p.per);
         const uint32_t col = beg / rows + j;
         const uint32_t start = j == 0 ? beg : col * rows, stop = min(end, (col + 1) * rows);
@@ -134,8 +134,8 @@ __device__ __forceinline__ void c2_item_rows(const FusedParams &p, size_t item, 
         ya = (int)(p.out_y0 + (empty ? 0u : start - col * rows));
         yb = (int)(p.out_y0 + (empty ? 0u : stop - col * rows));
     } else {
-        f = (uint32_t)(item / items_per_frame);
-        const uint32_t irem = (uint32_t)(item - (size_t)f * items_per_frame);
+        f = item / items_per_frame;
+        const uint32_t irem = item - f * items_per_frame;
         const int band = (int)(irem / p.strips);
         strip = (int)(irem - (uint32_t)band * p.strips);
         ya = (int)p.out_y0 + band * (int)p.band_rows, yb = min(ya + (int)p.band_rows, (int)p.out_y1);
@@ -195,14 +195,14 @@ __device__ __forceinline__ void v_pass_batch(const FusedParams &p, const float *
 // kParties = all threads that meet at the H-plane barriers (producing groups and this one).
 template <typename C, int R, bool GRAY, int C0, int NCH, int kParties>
 __device__ __forceinline__ void blur_only_consumer(const FusedParams &p, const float *Hb_base, int bcol, uint32_t items_per_frame,
-                                                   size_t total) {
+                                                   uint32_t total) {
     constexpr int kHbFloats = C::CH * C::RB * C::HS;
     const int W = (int)p.in.w, Himg = (int)p.in.h;
     const bool active = bcol < C::BW;
     uint32_t g = 0;
     bar_arrive(kB2Empty0, kParties);  // both H-plane slots start out empty
     bar_arrive(kB2Empty1, kParties);
-    for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
+    for (uint32_t item = blockIdx.x; item < total; item += gridDim.x) {
         uint32_t f;
         int strip, ya, yb;
         bool empty = false;
@@ -269,7 +269,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
     __syncthreads();
 
     const uint32_t items_per_frame = p.strips * p.bands;
-    const size_t total = p.balanced ? (size_t)gridDim.x * p.maxi : (size_t)items_per_frame * p.in.frames;
+#define C2_TOTAL_ITEMS() (p.balanced ? gridDim.x * p.maxi : items_per_frame * p.in.frames)  /* < 2^31: checked by the host */
     uint32_t g = 0;  // running batch counter: buffer slot = g & 1, identical sequence in all groups
     // threads meeting at the H-plane barriers: A + B, plus C when it shares the blur-only V pass (RGBA)
     constexpr int kABParties = (C::HGROUPS + C::VGROUPS) * kC2Group;  // producing + consuming groups
@@ -302,7 +302,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         constexpr int NRG = kHT / NC4;             // staging row groups (threads beyond NRG*NC4 idle)
         const int st_c4 = hid % NC4, st_rg = hid / NC4;
 
-        for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
+        for (uint32_t item = blockIdx.x, total = C2_TOTAL_ITEMS(); item < total; item += gridDim.x) {
             C2_ITEM_GEOMETRY();
             if (c2_empty) continue;  // (balanced partition: this CTA's range ended in an earlier strip)
             const uint8_t *in_frame = p.in.ptr + (size_t)f * p.in.frame_stride;
@@ -466,7 +466,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         // =========================== group B: V pass + quantise + intensity ===========================
         if constexpr (MODE == 1) {
             asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REGS_V));
-            blur_only_consumer<C, R, GRAY, 0, 2, kABParties>(p, Hb_base, tid - kC2Group, items_per_frame, total);
+            blur_only_consumer<C, R, GRAY, 0, 2, kABParties>(p, Hb_base, tid - kC2Group, items_per_frame, C2_TOTAL_ITEMS());
             return;
         }
         asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REGS_V));
@@ -476,7 +476,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         bar_arrive(kB2Empty0, 2 * kC2Group);  // both H-plane slots start out empty
         bar_arrive(kB2Empty1, 2 * kC2Group);
 
-        for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
+        for (uint32_t item = blockIdx.x, total = C2_TOTAL_ITEMS(); item < total; item += gridDim.x) {
             C2_ITEM_GEOMETRY();
             if (c2_empty) continue;  // (balanced partition: this CTA's range ended in an earlier strip)
             float2 vacc2[C::CH][R / 2];  // running outputs: slots (2i, 2i+1) packed, slot R-1 alone
@@ -565,7 +565,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         // =========================== group C: Sobel + store + SSIM ===========================
         if constexpr (MODE == 1) {  // RGBA blur: the V pass of channels 2 and 3 (after grayscale group C never gets here)
             asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REGS_V));
-            blur_only_consumer<C, R, GRAY, 2, 2, kABParties>(p, Hb_base, tid - 2 * kC2Group, items_per_frame, total);
+            blur_only_consumer<C, R, GRAY, 2, 2, kABParties>(p, Hb_base, tid - 2 * kC2Group, items_per_frame, C2_TOTAL_ITEMS());
             return;
         }
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(C::REGS_C));
@@ -588,10 +588,10 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         bar_arrive(kB2IEmpty0, 2 * kC2Group);  // both intensity slots start out empty
         bar_arrive(kB2IEmpty1, 2 * kC2Group);
 
-        for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
+        for (uint32_t item = blockIdx.x, total = C2_TOTAL_ITEMS(); item < total; item += gridDim.x) {
             C2_ITEM_GEOMETRY();
             if (c2_empty) {  // (balanced partition) nothing to do: the finalize pass still sums this slot
-                if (p.do_ssim && tc < 5) p.partials[item * 5 + tc] = 0.0;
+                if (p.do_ssim && tc < 5) p.partials[(size_t)item * 5 + tc] = 0.0;
                 continue;
             }
             const int x = x0 + 2 * cpa;                   // first column of the pair
@@ -740,7 +740,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                     if (lane == 0) red[k][warp] = sm;
                 }
                 bar_sync(kB2C, kC2Group);
-                if (tc < 5) p.partials[item * 5 + tc] = ((red[tc][0] + red[tc][1]) + red[tc][2]) + red[tc][3];
+                if (tc < 5) p.partials[(size_t)item * 5 + tc] = ((red[tc][0] + red[tc][1]) + red[tc][2]) + red[tc][3];
                 bar_sync(kB2C, kC2Group);
             }
         }
@@ -754,10 +754,10 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         bar_arrive(kB2IEmpty0, 2 * kC2Group);  // both intensity slots start out empty
         bar_arrive(kB2IEmpty1, 2 * kC2Group);
 
-        for (size_t item = blockIdx.x; item < total; item += gridDim.x) {
+        for (uint32_t item = blockIdx.x, total = C2_TOTAL_ITEMS(); item < total; item += gridDim.x) {
             C2_ITEM_GEOMETRY();
             if (c2_empty) {  // (balanced partition) nothing to do: the finalize pass still sums this slot
-                if (p.do_ssim && tc < 5) p.partials[item * 5 + tc] = 0.0;
+                if (p.do_ssim && tc < 5) p.partials[(size_t)item * 5 + tc] = 0.0;
                 continue;
             }
             const int x = x0 + tc;
@@ -880,13 +880,14 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                     if (lane == 0) red[k][warp] = s;
                 }
                 bar_sync(kB2C, kC2Group);
-                if (tc < 5) p.partials[item * 5 + tc] = ((red[tc][0] + red[tc][1]) + red[tc][2]) + red[tc][3];
+                if (tc < 5) p.partials[(size_t)item * 5 + tc] = ((red[tc][0] + red[tc][1]) + red[tc][2]) + red[tc][3];
                 bar_sync(kB2C, kC2Group);
             }
         }
 #endif  // NORM_C2_CPAIR
     }
 #undef C2_ITEM_GEOMETRY
+#undef C2_TOTAL_ITEMS
 }
 
 }  // namespace normk

@@ -551,6 +551,7 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
     fp.invert = p.inv ? 1u : 0u;
     fp.do_ssim = (d_ssim || d_moments) ? 1u : 0u;
     fp.ssim_y0 = std::max(y0, fp.out_y0), fp.ssim_y1 = std::max(fp.ssim_y0, std::min(y1, fp.out_y1));
+    if (grid_items >= (1ull << 31)) return fail(ctx, NORM_E_UNSUPPORTED, "more than 2^31 work items in one launch: split the batch");
     const unsigned grid = grid_for(ctx, grid_items, per_sm);
     // partial-sum slots per frame: one per work item (balanced: maxi per CTA, unused ones are written as zero)
     const uint32_t items_per_frame = fp.balanced ? grid * fp.maxi : fp.strips * fp.bands;
@@ -616,7 +617,9 @@ norm_status launch_fused_rx(norm_ctx *ctx, Slot &slot, const StagePlan &p, const
     }
 }
 
-#ifdef NORM_NO_EXTRA_RADII  // development builds: only the BASELINE radii (3, 7, 21, 39); a third of the compile time
+#if defined(NORM_NO_EXTRA_RADII) && defined(NORM_DEV_RADIUS)  // development builds: the BASELINE radii + one more
+#define NORM_EXTRA_RADII(X) X(NORM_DEV_RADIUS)
+#elif defined(NORM_NO_EXTRA_RADII)  // development builds: only the BASELINE radii (3, 7, 21, 39); a third of the compile time
 #define NORM_EXTRA_RADII(X)
 #else
 #define NORM_EXTRA_RADII(X) X(5) X(9) X(11) X(13) X(15) X(17) X(19) X(23) X(25) X(27) X(29) X(31) X(33) X(35) X(37)
