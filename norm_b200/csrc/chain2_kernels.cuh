@@ -40,7 +40,7 @@ constexpr int kC2Group = 128, kC2Threads = 3 * kC2Group;
 #endif
 #ifndef NORM_C2_REGS_H4
 #define NORM_C2_REGS_H4 64  // RGBA blur: group A (H pass of four channels); groups B and C share the rest
-#define NORM_C2_T4 8        // and its H-pass outputs per thread above r = 9
+#define NORM_C2_T4 10       // and its H-pass outputs per thread above r = 9 (10-column items: 252 per 21-row batch, 98 % of the lanes; 8 gave 315 = 82 %)
 #endif
 #ifndef NORM_C2_REGS_A
 #define NORM_C2_REGS_A 72   // measured best of 56/128/56, 64/112/64, 72/104/64, 72/112/56, 80/96/64, 80/104/56, 80/112/48:
@@ -61,7 +61,10 @@ struct Fused2Cfg {
     static constexpr int HALO = MODE == 0 ? 1 : 0;      // Sobel needs one blurred pixel around each output
     static constexpr int SW = 120;                      // output columns per strip
     static constexpr int BW = SW + 2 * HALO;            // blurred / intensity columns
-    static constexpr int T = (MODE == 1 && !GRAY && R > 9) ? NORM_C2_T4 : NORM_C2_T;  // H-pass outputs per thread (4-channel H pass: fewer, for registers)
+    // H-pass outputs per thread.  The 4-channel H pass of the RGBA blur takes 10 where that fills the rounds of 128
+    // threads (r = 21: 21 rows x 12 items = 252) and 8 where 8 does (r = 15, 17: 15 items per row give 225 / 255;
+    // measured 146 vs 141 / 139 Gpixel/s).
+    static constexpr int T = (MODE == 1 && !GRAY && R > 9) ? ((R == 15 || R == 17) ? 8 : NORM_C2_T4) : NORM_C2_T;
     // H-pass items per row: SEGS full items of T columns + one short item of TAIL columns.  T = 10 with the 21-row batch
     // gives 252 items for the group's 128 threads (two rounds, 98 % of the lanes busy) and no column is computed in vain.
     static constexpr int SEGS = (T % 4 == 0) ? (BW + T - 1) / T : BW / T;
