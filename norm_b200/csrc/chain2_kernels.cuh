@@ -38,6 +38,25 @@ constexpr int kC2Group = 128, kC2Threads = 3 * kC2Group;
 #ifndef NORM_C2_T
 #define NORM_C2_T 10
 #endif
+#ifndef NORM_C2_VSHIFT
+#define NORM_C2_VSHIFT 1      // group B (MODE 0): shift-form V pass, two rows per step (see the group's comment)
+#define NORM_C2_VSHIFT_RB 20  // its rows per batch (even; no longer tied to R)
+#define NORM_C2_VUNROLL 1     // two-row steps per loop trip
+#endif
+#ifndef NORM_C2_VSHIFT_MINR0
+// smallest radius that takes the shift form (measured, profiles/r02_radius_sweep.txt): below it the rotation's longer
+// batches (RB = 21 or R) win; above it the rotation's RB >= R no longer fits half an SM's shared memory
+#define NORM_C2_VSHIFT_MINR0 11   // chain on RGB
+#define NORM_C2_VSHIFT_MINR0G 35  // chain after grayscale (one H plane: the rotation fits two CTAs per SM up to r = 33)
+#define NORM_C2_VSHIFT_MINR1 9    // blur alone
+#endif
+#ifndef NORM_C2_NOTAIL
+#define NORM_C2_NOTAIL 0      // 1: whole H items only (the last one computes a few columns in vain) instead of the short item
+#endif
+#ifndef NORM_C2_NSH
+#define NORM_C2_NSH 2         // H-plane slots (A -> B ring) and intensity slots (B -> C ring) of the shift-form chain;
+#define NORM_C2_NSI 2         // 2 x NSH + 2 x NSI + 2 named barriers, at most 15
+#endif
 #ifndef NORM_C2_REGS_H4
 #define NORM_C2_REGS_H4 64  // RGBA blur: group A (H pass of four channels); groups B and C share the rest
 #define NORM_C2_T4 10       // and its H-pass outputs per thread above r = 9 (10-column items: 252 per 21-row batch, 98 % of the lanes; 8 gave 315 = 82 %)
@@ -64,13 +83,14 @@ struct Fused2Cfg {
     // H-pass outputs per thread.  The 4-channel H pass of the RGBA blur takes 10 where that fills the rounds of 128
     // threads (r = 21: 21 rows x 12 items = 252) and 8 where 8 does (r = 15, 17: 15 items per row give 225 / 255;
     // measured 146 vs 141 / 139 Gpixel/s).
-    static constexpr int T = (MODE == 1 && !GRAY && R > 9) ? ((R == 15 || R == 17) ? 8 : NORM_C2_T4) : NORM_C2_T;
+    static constexpr bool VSHIFT = NORM_C2_VSHIFT && !NORM_C2_CPAIR && R >= (MODE == 0 ? (GRAY ? NORM_C2_VSHIFT_MINR0G : NORM_C2_VSHIFT_MINR0) : NORM_C2_VSHIFT_MINR1);
+    static constexpr int T = (MODE == 1 && !GRAY && R > 9) ? ((!VSHIFT && (R == 15 || R == 17)) ? 8 : NORM_C2_T4) : NORM_C2_T;
     // H-pass items per row: SEGS full items of T columns + one short item of TAIL columns.  T = 10 with the 21-row batch
     // gives 252 items for the group's 128 threads (two rounds, 98 % of the lanes busy) and no column is computed in vain.
-    static constexpr int SEGS = (T % 4 == 0) ? (BW + T - 1) / T : BW / T;
-    static constexpr int TAIL = (T % 4 == 0) ? 0 : BW - SEGS * T;
+    static constexpr int SEGS = (T % 4 == 0 || NORM_C2_NOTAIL) ? (BW + T - 1) / T : BW / T;
+    static constexpr int TAIL = (T % 4 == 0 || NORM_C2_NOTAIL) ? 0 : BW - SEGS * T;
     static_assert(TAIL % 2 == 0 && TAIL >= 0 && TAIL <= 4, "short H item: an even number of columns");
-    static constexpr int HS = (BW + 3) / 4 * 4;         // 124: H plane row stride = columns actually stored
+    static constexpr int HS = ((TAIL ? BW : SEGS * T) + 3) / 4 * 4;  // 124: H plane row stride = columns actually stored
     static constexpr int HL = ((M + HALO) + 3) / 4 * 4; // staged left halo, 16-byte chunks
     static constexpr int OFF0 = HL - HALO - M;          // staged column of blurred column 0's first tap
     static constexpr int SRCW = (OFF0 + HS + R - 1 + 3) / 4 * 4;
@@ -78,7 +98,12 @@ struct Fused2Cfg {
     // rows per batch: a multiple of R, about 16.  The RGBA blur (four H planes) takes R itself from R = 13 on:
     // two times 13 or 15 rows would push its shared memory past half an SM and cost the second resident CTA
     // (measured: +11 % / +19 % at r = 13 / 15; the chain variants are faster with the longer batch).
-    static constexpr int RB = (R >= 13 && MODE == 1 && !GRAY) ? R : (R == 3 ? 21 : R * ((16 + R - 1) / R));
+    static constexpr int RB = VSHIFT ? NORM_C2_VSHIFT_RB : (R >= 13 && MODE == 1 && !GRAY) ? R : (R == 3 ? 21 : R * ((16 + R - 1) / R));
+    static_assert(!VSHIFT || RB % 2 == 0, "shift-form V pass: two rows per step");
+    // slots of the two hand-over rings and their named barriers (full / empty per slot); barrier 0 is __syncthreads
+    static constexpr int NSH = VSHIFT ? NORM_C2_NSH : 2, NSI = VSHIFT ? NORM_C2_NSI : 2;
+    static constexpr int BFULL = 1, BEMPTY = BFULL + NSH, BIFULL = BEMPTY + NSH, BIEMPTY = BIFULL + NSI, BA = BIEMPTY + NSI, BC = BA + 1;
+    static_assert(BC <= 15, "16 named barriers per CTA");
     static constexpr int CH = MODE == 0 ? (GRAY ? 1 : 3) : (GRAY ? 2 : 4);
     // MODE 1 after grayscale (channels y, alpha): groups A and C both run the H pass (one channel each, staging
     // shared) and group B runs the V pass of both and stores RGBA8.  MODE 1 on RGBA: group A runs the H pass
@@ -103,7 +128,7 @@ struct Fused2Cfg {
     static constexpr size_t kIstBytes = MODE == 0 ? (size_t)(RB + ICARRY) * IS * 4 : 0;
     static constexpr size_t kLutDBytes = (NORM_C2_CPAIR && MODE == 0) ? 256 * 8 : 0;  // luma of (c,c,c) as f64
     // + 64 words of slack: the last H segment's unused outputs read a few words past a staged row
-    static constexpr size_t kSmem = 2 * kStgBytes + 256 + 2 * kHbBytes + 2 * kIstBytes + 256 * 4 * 2 + 256 + kLutDBytes;
+    static constexpr size_t kSmem = 2 * kStgBytes + 256 + NSH * kHbBytes + NSI * kIstBytes + 256 * 4 * 2 + 256 + kLutDBytes;
     static_assert(T % 2 == 0 && HS % 4 == 0, "8- or 16-byte H stores");
 };
 
@@ -152,6 +177,37 @@ __device__ __forceinline__ void c2_item_rows(const FusedParams &p, uint32_t item
 template <typename C, int R, bool GRAY, int C0, int NCH>
 __device__ __forceinline__ void v_pass_batch(const FusedParams &p, const float *hp, int b, int NB, bool in_image, uint8_t *orow,
                                              float2 (*vacc2)[R / 2], float *vaccl) {
+    if constexpr (C::VSHIFT) {
+        // shift form (see group B of MODE 0): pair m of vacc2 = running outputs (first unfinished + 2m, + 2m + 1)
+        constexpr int NP = (R - 1) / 2;
+        for (int j = 0; j < C::RB; j += 2) {
+            uint32_t q0[NCH], q1[NCH];
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) {
+                const float ha = hp[((C0 + c) * C::RB + j) * C::HS], hb = hp[((C0 + c) * C::RB + j + 1) * C::HS];
+                const float2 h1 = make_float2(ha, ha), h2 = make_float2(hb, hb);
+                const float2 done = __ffma2_rn(p.tp[R], h2, __ffma2_rn(p.tp[R - 1], h1, vacc2[c][0]));
+#pragma unroll
+                for (int m = 1; m < NP; ++m)
+                    vacc2[c][m - 1] = __ffma2_rn(p.tp[R - 2 * m], h2, __ffma2_rn(p.tp[R - 1 - 2 * m], h1, vacc2[c][m]));
+                vacc2[c][NP - 1] = __ffma2_rn(p.tp[1], h2, __fmul2_rn(p.tp[0], h1));
+                q0[c] = __float_as_uint(__fadd_rn(done.x, 12582912.0f)) & 0xffu;
+                q1[c] = __float_as_uint(__fadd_rn(done.y, 12582912.0f)) & 0xffu;
+            }
+            const int n = b * C::RB + j - (R - 1);  // output row (relative to the band's first) completed by row j
+            uint8_t *px = orow + (ptrdiff_t)n * (ptrdiff_t)p.out.pitch;
+            const bool v0 = n >= 0 && n < NB && in_image, v1 = n + 1 >= 0 && n + 1 < NB && in_image;
+            if constexpr (GRAY) {
+                st_global_pred_u32(px, q0[0] * 0x010101u | (q0[NCH - 1] << 24), v0);
+                st_global_pred_u32(px + p.out.pitch, q1[0] * 0x010101u | (q1[NCH - 1] << 24), v1);
+            } else {
+                static_assert(NCH == 2, "RGBA: two channels per V-pass thread");
+                st_global_pred_u16(px + C0, q0[0] | (q0[1] << 8), v0);
+                st_global_pred_u16(px + p.out.pitch + C0, q1[0] | (q1[1] << 8), v1);
+            }
+        }
+        return;
+    }
 #pragma unroll
     for (int j = 0; j < C::RB; ++j) {
         uint32_t q[NCH];
@@ -247,8 +303,8 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
     __shared__ double red[5][4];
     uint32_t *stg_base = reinterpret_cast<uint32_t *>(smem_raw);
     float *Hb_base = reinterpret_cast<float *>(smem_raw + 2 * C::kStgBytes + 256);
-    float *Ist_base = reinterpret_cast<float *>(smem_raw + 2 * C::kStgBytes + 256 + 2 * C::kHbBytes);
-    float *lumaLut = reinterpret_cast<float *>(smem_raw + 2 * C::kStgBytes + 256 + 2 * C::kHbBytes + 2 * C::kIstBytes);
+    float *Ist_base = reinterpret_cast<float *>(smem_raw + 2 * C::kStgBytes + 256 + C::NSH * C::kHbBytes);
+    float *lumaLut = reinterpret_cast<float *>(smem_raw + 2 * C::kStgBytes + 256 + C::NSH * C::kHbBytes + C::NSI * C::kIstBytes);
     float *intLut = lumaLut + 256;
     uint8_t *flut = reinterpret_cast<uint8_t *>(intLut + 256);
     double *lumaLutD = reinterpret_cast<double *>(flut + 256);
@@ -273,7 +329,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
 
     const uint32_t items_per_frame = p.strips * p.bands;
 #define C2_TOTAL_ITEMS() (p.balanced ? gridDim.x * p.maxi : items_per_frame * p.in.frames)  /* < 2^31: checked by the host */
-    uint32_t g = 0;  // running batch counter: buffer slot = g & 1, identical sequence in all groups
+    uint32_t g = 0;  // running batch counter: ring slot = g mod (slots of the ring), identical sequence in all groups
     // threads meeting at the H-plane barriers: A + B, plus C when it shares the blur-only V pass (RGBA)
     constexpr int kABParties = (C::HGROUPS + C::VGROUPS) * kC2Group;  // producing + consuming groups
 
@@ -349,13 +405,13 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                 asm volatile("cp.async.commit_group;" ::: "memory");
             };
 
-            bar_sync(kB2A, kHT);  // previous item's last H pass is done with the staging buffers
+            bar_sync(C::BA, kHT);  // previous item's last H pass is done with the staging buffers
             stage_issue(0, 0);
 
             for (int b = 0; b < nbatch; ++b, ++g) {
                 uint32_t *stg = stg_base + (b & 1) * (C::RB * C::STG_STRIDE);
                 asm volatile("cp.async.wait_group 0;" ::: "memory");
-                bar_sync(kB2A, kHT);
+                bar_sync(C::BA, kHT);
                 if (b + 1 < nbatch) stage_issue(b + 1, (b + 1) & 1);
                 if (FRONT) {
                     if (st_rg < NRG) {
@@ -377,11 +433,11 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                             *cell = v;
                         }
                     }
-                    bar_sync(kB2A, kHT);
+                    bar_sync(C::BA, kHT);
                 }
 
-                const int slot = (int)(g & 1u);
-                bar_sync(kB2Empty0 + slot, kABParties);  // the consuming group(s) released this H-plane slot
+                const int slot = (int)(g % (uint32_t)C::NSH);
+                bar_sync(C::BEMPTY + slot, kABParties);  // the consuming group(s) released this H-plane slot
                 // one thread = (row, TT consecutive blurred columns) of the channels [c0, c0 + NCHH): the TT + R - 1 source
                 // pixels are read once and scattered into TT x NCHH register accumulators, outputs paired so that every
                 // tap is one FFMA2.  The first tap pair {t[0], 0} initialises both halves by a multiply.
@@ -457,7 +513,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                         }
                 }
                 __threadfence_block();
-                bar_arrive(kB2Full0 + slot, kABParties);
+                bar_arrive(C::BFULL + slot, kABParties);
             }
         }
     };
@@ -476,12 +532,74 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         const int bcol = tid - kC2Group;  // blurred column of the strip owned by this thread
         const bool active = bcol < C::BW;
 
-        bar_arrive(kB2Empty0, 2 * kC2Group);  // both H-plane slots start out empty
-        bar_arrive(kB2Empty1, 2 * kC2Group);
+        for (int sl = 0; sl < C::NSH; ++sl) bar_arrive(C::BEMPTY + sl, 2 * kC2Group);  // every H-plane slot starts out empty
 
         for (uint32_t item = blockIdx.x, total = C2_TOTAL_ITEMS(); item < total; item += gridDim.x) {
             C2_ITEM_GEOMETRY();
             if (c2_empty) continue;  // (balanced partition: this CTA's range ended in an earlier strip)
+            if constexpr (C::VSHIFT) {
+                // Shift form.  After the step for H rows (j, j+1) register pair m holds the running outputs (o, o+1) =
+                // first unfinished output + (2m, 2m+1); output o + i has taken taps 0 .. R-2-i.  One step feeds row j with
+                // tap pair tp[R-1-2m] and row j+1 with tp[R-2m] into pair m and writes the result to pair m-1: the
+                // three-operand FFMA2 shifts the window by two outputs for free, the taps are the same for every step, so
+                // the row loop is a real loop (a tenth of the unrolled rotation's code) and RB is not tied to R.
+                // Pair 0's result is the two outputs that completed with rows j and j+1; the top pair starts from
+                // nothing: tp[0] = {t[0], 0} by a multiply, then tp[1] = {t[1], t[0]}; tp[R] = {0, t[R-1]} adds an
+                // exact zero to the output that was complete after row j.  Same fma chain per output as the oracle's.
+                constexpr int NP = (R - 1) / 2;  // pairs kept between steps
+                constexpr int kVU = NORM_C2_VUNROLL;
+                float2 va[C::CH][NP];
+#pragma unroll
+                for (int c = 0; c < C::CH; ++c)
+#pragma unroll
+                    for (int m = 0; m < NP; ++m) va[c][m] = make_float2(0.0f, 0.0f);
+                for (int b = 0; b < nbatch; ++b, ++g) {
+                    const int slot = (int)(g % (uint32_t)C::NSH), islot = (int)(g % (uint32_t)C::NSI);
+                    bar_sync(C::BFULL + slot, 2 * kC2Group);      // H planes of this batch are ready
+                    bar_sync(C::BIEMPTY + islot, 2 * kC2Group);   // group C has released this intensity slot
+                    if (active) {
+                        const float *hp = Hb_base + slot * kHbFloats + bcol;
+                        float *ist = Ist_base + islot * kIstFloats + bcol;
+#pragma unroll kVU
+                        for (int j = 0; j < C::RB; j += 2) {
+                            float v0[C::CH], v1[C::CH];
+#pragma unroll
+                            for (int c = 0; c < C::CH; ++c) {
+                                const float ha = hp[(c * C::RB + j) * C::HS], hb = hp[(c * C::RB + j + 1) * C::HS];
+                                const float2 h1 = make_float2(ha, ha), h2 = make_float2(hb, hb);
+                                const float2 done = __ffma2_rn(p.tp[R], h2, __ffma2_rn(p.tp[R - 1], h1, va[c][0]));
+#pragma unroll
+                                for (int m = 1; m < NP; ++m)
+                                    va[c][m - 1] = __ffma2_rn(p.tp[R - 2 * m], h2, __ffma2_rn(p.tp[R - 1 - 2 * m], h1, va[c][m]));
+                                va[c][NP - 1] = __ffma2_rn(p.tp[1], h2, __fmul2_rn(p.tp[0], h1));
+                                // round-half-even through the 1.5*2^23 trick: the quantised byte sits in the low
+                                // mantissa bits of (o + 1.5*2^23)
+                                v0[c] = __fadd_rn(done.x, 12582912.0f), v1[c] = __fadd_rn(done.y, 12582912.0f);
+                            }
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const float *v = e ? v1 : v0;
+                                float I;
+                                if (GRAY) {
+                                    I = intLut[__float_as_uint(v[0]) & 0xffu];
+                                } else {
+                                    // r^2 + g^2 + b^2 of the three quantised bytes: pack them (two PRMT) and take one byte
+                                    // dot product; the radicand is an integer < 2^18, so its conversion is exact and
+                                    // equals the float sum of squares the oracle forms
+                                    const uint32_t rg = __byte_perm(__float_as_uint(v[0]), __float_as_uint(v[C::CH > 1 ? 1 : 0]), 0x7740);
+                                    const uint32_t rgb = __byte_perm(rg, __float_as_uint(v[C::CH - 1]), 0x5410);
+                                    I = sqrt_rn_inrange0((float)__dp4a(rgb, rgb, 0u));
+                                }
+                                ist[(j + e) * C::IS] = I;
+                            }
+                        }
+                    }
+                    __threadfence_block();
+                    bar_arrive(C::BEMPTY + slot, 2 * kC2Group);   // done reading the H planes
+                    bar_arrive(C::BIFULL + islot, 2 * kC2Group);   // intensity rows of this batch are ready
+                }
+                continue;
+            }
             float2 vacc2[C::CH][R / 2];  // running outputs: slots (2i, 2i+1) packed, slot R-1 alone
             float vaccl[C::CH];
 #if NORM_C2_CPAIR
@@ -494,18 +612,18 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                 for (int i = 0; i < R / 2; ++i) vacc2[c][i] = make_float2(0.0f, 0.0f);
             }
             for (int b = 0; b < nbatch; ++b, ++g) {
-                const int slot = (int)(g & 1u);
-                bar_sync(kB2Full0 + slot, 2 * kC2Group);    // H planes of this batch are ready
-                bar_sync(kB2IEmpty0 + slot, 2 * kC2Group);  // group C has released this intensity slot
+                const int slot = (int)(g % (uint32_t)C::NSH), islot = (int)(g % (uint32_t)C::NSI);
+                bar_sync(C::BFULL + slot, 2 * kC2Group);      // H planes of this batch are ready
+                bar_sync(C::BIEMPTY + islot, 2 * kC2Group);   // group C has released this intensity slot
                 if (active) {
                     const float *hp = Hb_base + slot * kHbFloats + bcol;
 #if NORM_C2_CPAIR
                     // blurred column bcol lives at index bcol + 1 (keeps group C's pixel pairs 8-byte aligned);
                     // rows -2, -1 of the slot = the previous batch's last two rows
-                    float *ist = Ist_base + slot * kIstFloats + C::ICARRY * C::IS + bcol + 1;
+                    float *ist = Ist_base + islot * kIstFloats + C::ICARRY * C::IS + bcol + 1;
                     ist[-2 * C::IS] = icarry0, ist[-1 * C::IS] = icarry1;
 #else
-                    float *ist = Ist_base + slot * kIstFloats + bcol;
+                    float *ist = Ist_base + islot * kIstFloats + bcol;
 #endif
 #pragma unroll
                     for (int j = 0; j < C::RB; ++j) {
@@ -560,8 +678,8 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                     }
                 }
                 __threadfence_block();
-                bar_arrive(kB2Empty0 + slot, 2 * kC2Group);   // done reading the H planes
-                bar_arrive(kB2IFull0 + slot, 2 * kC2Group);   // intensity rows of this batch are ready
+                bar_arrive(C::BEMPTY + slot, 2 * kC2Group);   // done reading the H planes
+                bar_arrive(C::BIFULL + islot, 2 * kC2Group);   // intensity rows of this batch are ready
             }
         }
     } else {
@@ -588,8 +706,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         uint32_t lutd = (uint32_t)__cvta_generic_to_shared(lumaLutD) - (kMagicBits << 3);
         asm volatile("" : "+r"(lutd));
 
-        bar_arrive(kB2IEmpty0, 2 * kC2Group);  // both intensity slots start out empty
-        bar_arrive(kB2IEmpty1, 2 * kC2Group);
+        for (int sl = 0; sl < C::NSI; ++sl) bar_arrive(C::BIEMPTY + sl, 2 * kC2Group);  // every intensity slot starts out empty
 
         for (uint32_t item = blockIdx.x, total = C2_TOTAL_ITEMS(); item < total; item += gridDim.x) {
             C2_ITEM_GEOMETRY();
@@ -621,9 +738,9 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
             };
 
             for (int b = 0; b < nbatch; ++b, ++g) {
-                const int slot = (int)(g & 1u);
-                bar_sync(kB2IFull0 + slot, 2 * kC2Group);
-                const float *ist = Ist_base + slot * kIstFloats + C::ICARRY * C::IS;  // batch row j at ist + j*IS
+                const int islot = (int)(g % (uint32_t)C::NSI);
+                bar_sync(C::BIFULL + islot, 2 * kC2Group);
+                const float *ist = Ist_base + islot * kIstFloats + C::ICARRY * C::IS;  // batch row j at ist + j*IS
                 const int n0 = b * C::RB - (R - 1);   // blurred row (relative to o_lo) that batch row 0 completes
                 const int yfirst = o_lo + n0 - 1;     // output row emitted when batch row 0 arrives
                 // this warp's rows [JA, JB) of the batch; the two warp pairs swap the longer share from batch to batch
@@ -734,7 +851,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                     }
                 }
                 __threadfence_block();
-                bar_arrive(kB2IEmpty0 + slot, 2 * kC2Group);
+                bar_arrive(C::BIEMPTY + islot, 2 * kC2Group);
             }
             if (p.do_ssim) {
 #pragma unroll
@@ -742,9 +859,9 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                     const double sm = warp_sum(act ? m5[k] : 0.0);
                     if (lane == 0) red[k][warp] = sm;
                 }
-                bar_sync(kB2C, kC2Group);
+                bar_sync(C::BC, kC2Group);
                 if (tc < 5) p.partials[(size_t)item * 5 + tc] = ((red[tc][0] + red[tc][1]) + red[tc][2]) + red[tc][3];
-                bar_sync(kB2C, kC2Group);
+                bar_sync(C::BC, kC2Group);
             }
         }
 #else
@@ -754,8 +871,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         uint32_t lut_biased = (uint32_t)__cvta_generic_to_shared(lumaLut) - (kMagicBits << 2);
         asm volatile("" : "+r"(lut_biased));  // keep it in a register: one LEA per lookup instead of LEA + add
 
-        bar_arrive(kB2IEmpty0, 2 * kC2Group);  // both intensity slots start out empty
-        bar_arrive(kB2IEmpty1, 2 * kC2Group);
+        for (int sl = 0; sl < C::NSI; ++sl) bar_arrive(C::BIEMPTY + sl, 2 * kC2Group);  // every intensity slot starts out empty
 
         for (uint32_t item = blockIdx.x, total = C2_TOTAL_ITEMS(); item < total; item += gridDim.x) {
             C2_ITEM_GEOMETRY();
@@ -813,13 +929,13 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
 #define C2_ROWTEST (ssim_on && (uint32_t)(y - (int)p.ssim_y0) < p.ssim_y1 - p.ssim_y0)
 
             for (int b = 0; b < nbatch; ++b, ++g) {
-                const int slot = (int)(g & 1u);
+                const int islot = (int)(g % (uint32_t)C::NSI);
                 // rows of this batch whose blurred output exists: n = b*RB + j - (R-1) in [0, NB)
                 const int j_lo = max(0, (R - 1) - b * C::RB), j_hi = min(C::RB, NB + (R - 1) - b * C::RB);
                 // first row of this batch that completes an OWNED output row (y = o-1 >= ya)
                 const int j_e = max(j_lo, (ya + 1 - o_lo) + (R - 1) - b * C::RB);
-                bar_sync(kB2IFull0 + slot, 2 * kC2Group);
-                const float *ist = Ist_base + slot * kIstFloats;
+                bar_sync(C::BIFULL + islot, 2 * kC2Group);
+                const float *ist = Ist_base + islot * kIstFloats;
                 int j = j_lo;
                 // rows that only fill the window (at most two per item)
                 for (; j < min(j_e, j_hi); ++j) {
@@ -869,7 +985,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                     w1l = w2l, w1c = w2c, w1r = w2r;
                 }
                 __threadfence_block();
-                bar_arrive(kB2IEmpty0 + slot, 2 * kC2Group);
+                bar_arrive(C::BIEMPTY + islot, 2 * kC2Group);
             }
             // bottom edge of the image: row H-1 reads row H (clamped) = row H-1
             if (yb == Himg) C2_EMIT(w1l, w1c, w1r, w1l, w1r, w0l, w0c, w0r, sp0, C2_ROWTEST);
@@ -882,9 +998,9 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
                     const double s = warp_sum(m5[k]);
                     if (lane == 0) red[k][warp] = s;
                 }
-                bar_sync(kB2C, kC2Group);
+                bar_sync(C::BC, kC2Group);
                 if (tc < 5) p.partials[(size_t)item * 5 + tc] = ((red[tc][0] + red[tc][1]) + red[tc][2]) + red[tc][3];
-                bar_sync(kB2C, kC2Group);
+                bar_sync(C::BC, kC2Group);
             }
         }
 #endif  // NORM_C2_CPAIR

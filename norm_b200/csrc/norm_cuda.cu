@@ -571,11 +571,11 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
 }
 
 #ifndef NORM_GEN2_RGB_MAX_R
-#define NORM_GEN2_RGB_MAX_R 23   // chain on RGB: group B keeps 3 x R running outputs in registers and R + 1 tap pairs in
+#define NORM_GEN2_RGB_MAX_R 31   // chain on RGB: group B keeps 3 x R running outputs in registers and R + 1 tap pairs in
                                  // the 63 uniform registers; from r = 25 on the pairs no longer fit and the kernel spills
 #endif
 #ifndef NORM_GEN2_RGBA_MAX_R
-#define NORM_GEN2_RGBA_MAX_R 27  // blur of four channels: groups B and C keep 2 x R running outputs each (spills from r = 29)
+#define NORM_GEN2_RGBA_MAX_R 39  // blur of four channels: groups B and C keep 2 x R running outputs each (spills from r = 29)
 #endif
 
 template <int R>
