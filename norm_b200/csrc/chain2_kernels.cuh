@@ -4,21 +4,26 @@
 // decomposition.  Work item = (frame, row band, 120-column strip); the CTA (12 warps) walks
 // down the strip in batches of RB rows with three groups working on different batches at once:
 //
-//   group A (warps 0-3)   cp.async staging of RB source rows (ClampToEdge), optional in-place
-//                         front stage, H pass: thread = (row, 12-column segment), 12 x CH
-//                         outputs in registers, every tap one FFMA2, 16-byte smem stores.
-//   group B (warps 4-7)   thread = one blurred column for ALL channels: V pass with R running
-//                         outputs per channel in registers across batches (static rotation,
-//                         RB % R == 0), quantise, intensity sqrt(r^2+g^2+b^2) -> one f32 / pixel.
-//   group C (warps 8-11)  thread = one output column: 3x3 Sobel on the intensity rows (window
-//                         kept in registers, rotated by a 3-row static unroll), RGBA8 store,
-//                         f64 SSIM moments against the source pixel (prefetched one row ahead).
+//   group A   cp.async staging of RB source rows (ClampToEdge), optional in-place front stage,
+//             H pass: thread = (row, T-column item), T x CH outputs in registers, every tap one
+//             FFMA2, 8- or 16-byte smem stores.
+//   group B   thread = one blurred column for ALL channels: V pass with the running outputs of
+//             each channel in registers across batches, quantise, intensity sqrt(r^2+g^2+b^2)
+//             -> one f32 / pixel.  Two forms of the V pass: the rotation (row loop unrolled over
+//             RB rows, RB % R == 0, output slot s takes tap (row - s) mod R) for small radii, and
+//             the shift form (two rows per step, the outputs move down one register pair per
+//             step through the three-operand FFMA2; RB free) for the rest.
+//   group C   thread = one output column: 3x3 Sobel on the intensity rows (window kept in
+//             registers, rotated by a 3-row static unroll), RGBA8 store, f64 SSIM moments
+//             against the source pixel (prefetched three rows ahead).
+//   (roles -> warps: see the permutation at the top of the kernel)
 //
-// A->B hand over double-buffered f32 H planes, B->C double-buffered intensity rows; each
-// hand-off is a full/empty pair of named barriers per slot, so no group ever waits on more
-// than its neighbour.  Register budgets follow the roles (setmaxnreg): B holds 3*R
-// accumulators and takes 112 registers, A keeps 72 (no spills in the H pass), C gives its share up (56).
-// Instantiated for R <= 21 on RGB (3*21 accumulators); wider radii use chain_fused_kernel.
+// A->B hand over f32 H planes, B->C intensity rows, each through a ring of slots with a
+// full/empty pair of named barriers per slot, so no group ever waits on more than its
+// neighbour.  Register budgets follow the roles (setmaxnreg, two CTAs per SM: 3 x 80 per
+// thread trio): B takes 112, A keeps 72 (no spills in the H pass), C gives its share up (56).
+// RGB chains from r = 33 and the RGBA blur from r = 37 hold more running outputs than that
+// allows and run one CTA per SM without re-division (Fused2Cfg::BIG).
 #pragma once
 #include "chain_kernels.cuh"
 
@@ -43,11 +48,30 @@ constexpr int kC2Group = 128, kC2Threads = 3 * kC2Group;
 #define NORM_C2_VSHIFT_RB 20  // its rows per batch (even; no longer tied to R)
 #define NORM_C2_VUNROLL 1     // two-row steps per loop trip
 #endif
+#ifndef NORM_C2_VSHIFT_RBG
+#define NORM_C2_VSHIFT_RBG 32 // ... in the chain after grayscale (one H plane: more rows fit; r = 21: 156 -> 162 Gpixel/s)
+#endif
+#ifndef NORM_C2_VSHIFT_MINR0G
+#define NORM_C2_VSHIFT_MINR0G 17  // chain after grayscale: the rotation (RB = 2 x R up to r = 15) wins below
+#endif
+#ifndef NORM_C2_BIG_MINR
+#define NORM_C2_BIG_MINR 33   // RGB chain from this radius on: one CTA per SM, see Fused2Cfg::BIG
+#endif
+#ifndef NORM_C2_BIG_MINR1
+#define NORM_C2_BIG_MINR1 37  // ... and the RGBA blur (2 x 2 x (R - 1) running outputs in groups B and C)
+#endif
+#ifndef NORM_C2_BIG_T1
+#define NORM_C2_BIG_T1 8      // (8-column items: the unrolled H item of four channels stays below ~900 FFMA2, beyond which
+#define NORM_C2_BIG_RB1 34    //  nvcc leaves the column loop rolled, with dynamic tap indices); 15 items per row: 510 for four rounds
+#endif
+#ifndef NORM_C2_BIG_T
+#define NORM_C2_BIG_T 12      // its H-pass outputs per thread and rows per batch (11 items per row: 374 for three rounds of 128)
+#define NORM_C2_BIG_RB 34
+#endif
 #ifndef NORM_C2_VSHIFT_MINR0
 // smallest radius that takes the shift form (measured, profiles/r02_radius_sweep.txt): below it the rotation's longer
 // batches (RB = 21 or R) win; above it the rotation's RB >= R no longer fits half an SM's shared memory
 #define NORM_C2_VSHIFT_MINR0 11   // chain on RGB
-#define NORM_C2_VSHIFT_MINR0G 35  // chain after grayscale (one H plane: the rotation fits two CTAs per SM up to r = 33)
 #define NORM_C2_VSHIFT_MINR1 9    // blur alone
 #endif
 #ifndef NORM_C2_NOTAIL
@@ -84,7 +108,14 @@ struct Fused2Cfg {
     // threads (r = 21: 21 rows x 12 items = 252) and 8 where 8 does (r = 15, 17: 15 items per row give 225 / 255;
     // measured 146 vs 141 / 139 Gpixel/s).
     static constexpr bool VSHIFT = NORM_C2_VSHIFT && !NORM_C2_CPAIR && R >= (MODE == 0 ? (GRAY ? NORM_C2_VSHIFT_MINR0G : NORM_C2_VSHIFT_MINR0) : NORM_C2_VSHIFT_MINR1);
-    static constexpr int T = (MODE == 1 && !GRAY && R > 9) ? ((!VSHIFT && (R == 15 || R == 17)) ? 8 : NORM_C2_T4) : NORM_C2_T;
+    // RGB chain at the largest radii: 3 x (R - 1) running outputs (114 at r = 39) exceed what a thread of group B can
+    // hold when two CTAs share an SM (3 x 80 registers per thread trio).  Those radii run ONE CTA per SM with up to 168
+    // registers per thread and no re-division, and spend the freed shared memory and registers on longer batches and
+    // 16-column H items (fewer unpacks per pixel: (T + R - 1) / T).
+    static constexpr bool BIG = VSHIFT && !GRAY && R >= (MODE == 0 ? NORM_C2_BIG_MINR : NORM_C2_BIG_MINR1);
+    static constexpr int CTAS = BIG ? 1 : 2;            // resident CTAs per SM the kernel is built for
+    static constexpr int REGS_LAUNCH = BIG ? 168 : 80;  // registers per thread at launch (__launch_bounds__)
+    static constexpr int T = BIG ? (MODE == 0 ? NORM_C2_BIG_T : NORM_C2_BIG_T1) : (MODE == 1 && !GRAY && R > 9) ? ((!VSHIFT && (R == 15 || R == 17)) ? 8 : NORM_C2_T4) : NORM_C2_T;
     // H-pass items per row: SEGS full items of T columns + one short item of TAIL columns.  T = 10 with the 21-row batch
     // gives 252 items for the group's 128 threads (two rounds, 98 % of the lanes busy) and no column is computed in vain.
     static constexpr int SEGS = (T % 4 == 0 || NORM_C2_NOTAIL) ? (BW + T - 1) / T : BW / T;
@@ -98,7 +129,7 @@ struct Fused2Cfg {
     // rows per batch: a multiple of R, about 16.  The RGBA blur (four H planes) takes R itself from R = 13 on:
     // two times 13 or 15 rows would push its shared memory past half an SM and cost the second resident CTA
     // (measured: +11 % / +19 % at r = 13 / 15; the chain variants are faster with the longer batch).
-    static constexpr int RB = VSHIFT ? NORM_C2_VSHIFT_RB : (R >= 13 && MODE == 1 && !GRAY) ? R : (R == 3 ? 21 : R * ((16 + R - 1) / R));
+    static constexpr int RB = BIG ? (MODE == 0 ? NORM_C2_BIG_RB : NORM_C2_BIG_RB1) : VSHIFT ? ((MODE == 0 && GRAY) ? NORM_C2_VSHIFT_RBG : NORM_C2_VSHIFT_RB) : (R >= 13 && MODE == 1 && !GRAY) ? R : (R == 3 ? 21 : R * ((16 + R - 1) / R));
     static_assert(!VSHIFT || RB % 2 == 0, "shift-form V pass: two rows per step");
     // slots of the two hand-over rings and their named barriers (full / empty per slot); barrier 0 is __syncthreads
     static constexpr int NSH = VSHIFT ? NORM_C2_NSH : 2, NSI = VSHIFT ? NORM_C2_NSI : 2;
@@ -114,9 +145,9 @@ struct Fused2Cfg {
     static constexpr int CH_A = (MODE == 1 && GRAY) ? 1 : CH;   // channels of group A's H pass (from 0)
     static constexpr int HTHREADS = HGROUPS * 128;
     // register budgets (setmaxnreg), summing to 3 x 80
-    static constexpr int REGS_H = MODE == 1 ? (GRAY ? 56 : NORM_C2_REGS_H4) : NORM_C2_REGS_A;              // MODE 1 + GRAY: two H groups
-    static constexpr int REGS_V = MODE == 1 ? (GRAY ? 128 : (240 - NORM_C2_REGS_H4) / 2) : NORM_C2_REGS_B;
-    static constexpr int REGS_C = MODE == 0 ? 240 - REGS_H - REGS_V : 0;
+    static constexpr int REGS_H = BIG ? 168 : MODE == 1 ? (GRAY ? 56 : NORM_C2_REGS_H4) : NORM_C2_REGS_A;              // MODE 1 + GRAY: two H groups
+    static constexpr int REGS_V = BIG ? 168 : MODE == 1 ? (GRAY ? 128 : (240 - NORM_C2_REGS_H4) / 2) : NORM_C2_REGS_B;
+    static constexpr int REGS_C = BIG ? 168 : MODE == 0 ? 240 - REGS_H - REGS_V : 0;
     // source byte of channel c: MODE 1 + GRAY blurs (y, alpha) = bytes (0, 3)
     __host__ __device__ static constexpr int chan_byte(int c) { return (MODE == 1 && GRAY && c == 1) ? 3 : c; }
     static constexpr int IS = 128;                      // intensity row stride
@@ -297,7 +328,7 @@ __device__ __forceinline__ void blur_only_consumer(const FusedParams &p, const f
 }
 
 template <int R, bool GRAY, bool FRONT, int MODE = 0>
-__global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __grid_constant__ FusedParams p) {
+__global__ void __launch_bounds__(kC2Threads, (Fused2Cfg<R, GRAY, MODE>::CTAS)) chain_fused2_kernel(const __grid_constant__ FusedParams p) {
     using C = Fused2Cfg<R, GRAY, MODE>;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     __shared__ double red[5][4];
@@ -354,7 +385,7 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
         constexpr int ROLE = decltype(role_tag)::value;
         constexpr int c0 = ROLE == 0 ? 0 : C::CH - 1;
         constexpr int NCHH = ROLE == 0 ? C::CH_A : 1;
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(C::REGS_H));
+        if constexpr (!C::BIG) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(C::REGS_H));
         constexpr int kHT = C::HTHREADS;
         const int hid = tid < kC2Group ? tid : tid - kC2Group;  // index within the H-pass threads
         constexpr int NC4 = C::SRCW / 4;           // 16-byte chunks per staged row
@@ -524,11 +555,11 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
     } else if (tid < 2 * kC2Group) {
         // =========================== group B: V pass + quantise + intensity ===========================
         if constexpr (MODE == 1) {
-            asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REGS_V));
+            if constexpr (!C::BIG) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REGS_V));
             blur_only_consumer<C, R, GRAY, 0, 2, kABParties>(p, Hb_base, tid - kC2Group, items_per_frame, C2_TOTAL_ITEMS());
             return;
         }
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REGS_V));
+        if constexpr (!C::BIG) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REGS_V));
         const int bcol = tid - kC2Group;  // blurred column of the strip owned by this thread
         const bool active = bcol < C::BW;
 
@@ -685,11 +716,11 @@ __global__ void __launch_bounds__(kC2Threads, 2) chain_fused2_kernel(const __gri
     } else {
         // =========================== group C: Sobel + store + SSIM ===========================
         if constexpr (MODE == 1) {  // RGBA blur: the V pass of channels 2 and 3 (after grayscale group C never gets here)
-            asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REGS_V));
+            if constexpr (!C::BIG) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REGS_V));
             blur_only_consumer<C, R, GRAY, 2, 2, kABParties>(p, Hb_base, tid - 2 * kC2Group, items_per_frame, C2_TOTAL_ITEMS());
             return;
         }
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(C::REGS_C));
+        if constexpr (!C::BIG) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(C::REGS_C));
 #if NORM_C2_CPAIR
         // Pair version.  A thread owns TWO adjacent output columns (one 8-byte store, one 8-byte source load per row);
         // warps 0/1 of the group take the column halves of batch rows [0, JH), warps 2/3 those of rows [JH, RB), so all

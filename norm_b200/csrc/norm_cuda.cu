@@ -480,7 +480,7 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
     constexpr int kThreads = GEN == 1 ? kFusedThreads : kC2Threads;
     if constexpr (GEN != 1) {
         // The pipelined kernel re-divides its registers between the warp groups (setmaxnreg) on the assumption that it
-        // was launched with exactly 80 per thread: with fewer, the groups that ask for more would wait forever for
+        // was launched with exactly C::REGS_LAUNCH (80; 168 for the one-CTA-per-SM radii) per thread: with fewer, the groups that ask for more would wait forever for
         // registers nobody releases.  Checked once per instantiation instead of trusted.
         static int regs = -1;  // (per template instantiation)
         if (regs < 0) {
@@ -488,9 +488,10 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
             CU_TRY(ctx, cudaFuncGetAttributes(&fa, kern));
             regs = fa.numRegs;
         }
-        if (regs != 80)
+        if (!C::BIG && regs != C::REGS_LAUNCH)  // (the one-CTA-per-SM configuration does not re-divide its registers)
             return fail(ctx, NORM_E_UNSUPPORTED, "fused kernel was built with " + std::to_string(regs) +
-                        " registers per thread; its setmaxnreg budgets need exactly 80 (check the nvcc flags)");
+                        " registers per thread; its setmaxnreg budgets need exactly " + std::to_string(C::REGS_LAUNCH) +
+                        " (check the nvcc flags)");
     }
     CU_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kSmem));
     int per_sm = 1;
@@ -570,19 +571,21 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
     return NORM_OK;
 }
 
+// Largest radius of the pipelined kernel (development builds lower these to fall back to the first-generation kernels).
+// Every radius the reference's UI reaches runs on it: the shift-form V pass keeps 3 x (R - 1) (chain on RGB) or
+// 2 x 2 x (R - 1) (RGBA blur, groups B and C) running outputs in registers, with one CTA per SM from r = 33 / 37.
 #ifndef NORM_GEN2_RGB_MAX_R
-#define NORM_GEN2_RGB_MAX_R 31   // chain on RGB: group B keeps 3 x R running outputs in registers and R + 1 tap pairs in
-                                 // the 63 uniform registers; from r = 25 on the pairs no longer fit and the kernel spills
+#define NORM_GEN2_RGB_MAX_R 39
 #endif
 #ifndef NORM_GEN2_RGBA_MAX_R
-#define NORM_GEN2_RGBA_MAX_R 39  // blur of four channels: groups B and C keep 2 x R running outputs each (spills from r = 29)
+#define NORM_GEN2_RGBA_MAX_R 39
 #endif
 
 template <int R>
 norm_status launch_fused_r(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
                            double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1) {
     // second-generation kernel (column-owner consumer) where its register budget allows
-    // (group B keeps CH*R running outputs in registers: any radius on one channel, R <= 23 on RGB)
+    // (the first-generation kernel stays selectable, NORM_CUDA_FUSED_GEN=1, at the BASELINE radii: cross-check tests)
     if constexpr (R <= NORM_GEN2_RGB_MAX_R) {
         if (ctx->fused_gen != 1) {
             if (p.gray) return launch_fused<R, true, true, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
@@ -598,8 +601,7 @@ norm_status launch_fused_r(norm_ctx *ctx, Slot &slot, const StagePlan &p, const 
 }
 
 // The other radii the reference's UI can reach (odd, 3..39 in steps of 2, feature_uniform.rs:66-84): pipelined
-// kernel only (the first-generation kernel is not instantiated for them, except on RGB above r = 21 where the
-// pipelined kernel's 3 x R running outputs do not fit).
+// kernel only (the first-generation kernel is not instantiated for them unless NORM_GEN2_RGB_MAX_R is lowered).
 template <int R>
 norm_status launch_fused_rx(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
                             double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1, bool *fused) {
