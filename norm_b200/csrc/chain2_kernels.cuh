@@ -513,35 +513,20 @@ __global__ void __launch_bounds__(kC2Threads, (Fused2Cfg<R, GRAY, MODE>::CTAS)) 
                 for (int it = hid & (kC2Group - 1); it < C::RB * C::SEGS; it += kC2Group)
                     h_item(std::integral_constant<int, C::T>{}, it / C::SEGS, (it % C::SEGS) * C::T);
                 if constexpr (C::TAIL > 0) {
-                    // the columns left over (the Sobel halo makes BW = 122): one short item per row, on one warp of the
-                    // group, a different one from batch to batch so that the four sub-partitions share them
-                    const int hl = hid & (kC2Group - 1);
-                    // scalar FMAs with the taps as constant-bank operands: the tap PAIRS stay the only uniform-register
-                    // resident set (a second use of them here makes the compiler copy them into vector registers)
-                    if ((hl >> 5) == (b & 3))
-                        for (int j = hl & 31; j < C::RB; j += 32) {
-                            const uint32_t *sp = stg + j * C::STG_STRIDE + C::OFF0 + C::SEGS * C::T;
-                            float acc[C::TAIL][NCHH];
+                    // the columns left over (the Sobel halo makes BW = 122): one thread per (row, column, channel) of them,
+                    // spread over the whole group, so the leftovers lengthen every warp's batch by one short pass of R
+                    // taps instead of one warp's by a whole item (measured +0.6 % at r = 21; scalar FMAs, taps as constant-bank operands: a second
+                    // user of the tap PAIRS would push them out of the uniform registers)
+                    constexpr int UNITS = C::RB * C::TAIL * NCHH;
+                    for (int u = hid & (kC2Group - 1); u < UNITS; u += kC2Group) {
+                        const int j = u / (C::TAIL * NCHH), rem = u - j * (C::TAIL * NCHH), o = rem / NCHH, c = rem - o * NCHH;
+                        const uint32_t *sp = stg + j * C::STG_STRIDE + C::OFF0 + C::SEGS * C::T + o;
+                        const uint32_t sel = 0x4440u | (uint32_t)C::chan_byte(c0 + c);  // byte -> low byte, zeros above
+                        float acc = __fmul_rn(p.taps.t[0], __uint2float_rn(__byte_perm(sp[0], 0u, sel)));
 #pragma unroll
-                            for (int jj = 0; jj < C::TAIL + R - 1; ++jj) {
-                                const uint32_t px = sp[jj];
-#pragma unroll
-                                for (int c = 0; c < NCHH; ++c) {
-                                    const float v = byte_f(px, C::chan_byte(c0 + c));
-#pragma unroll
-                                    for (int o = 0; o < C::TAIL; ++o) {
-                                        const int k = jj - o;
-                                        if (k == 0) acc[o][c] = __fmul_rn(p.taps.t[0], v);
-                                        else if (k > 0 && k < R) acc[o][c] = __fmaf_rn(p.taps.t[k], v, acc[o][c]);
-                                    }
-                                }
-                            }
-                            float *hp = Hb_base + slot * kHbFloats + j * C::HS + C::SEGS * C::T;
-#pragma unroll
-                            for (int c = 0; c < NCHH; ++c)
-#pragma unroll
-                                for (int o = 0; o < C::TAIL; ++o) hp[(c0 + c) * (C::RB * C::HS) + o] = acc[o][c];
-                        }
+                        for (int k = 1; k < R; ++k) acc = __fmaf_rn(p.taps.t[k], __uint2float_rn(__byte_perm(sp[k], 0u, sel)), acc);
+                        Hb_base[slot * kHbFloats + (c0 + c) * (C::RB * C::HS) + j * C::HS + C::SEGS * C::T + o] = acc;
+                    }
                 }
                 __threadfence_block();
                 bar_arrive(C::BFULL + slot, kABParties);
