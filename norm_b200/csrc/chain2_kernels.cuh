@@ -74,6 +74,9 @@ constexpr int kC2Group = 128, kC2Threads = 3 * kC2Group;
 #define NORM_C2_VSHIFT_MINR0 11   // chain on RGB
 #define NORM_C2_VSHIFT_MINR1 9    // blur alone
 #endif
+#ifndef NORM_C2_ROT21
+#define NORM_C2_ROT21 1       // the RGB chain at r = 21 keeps the rotation: its 21-row batch gives 252 H items = 98 % of group A's lanes (20 rows: 94 %); measured 134.3 vs 131.8 Gpixel/s
+#endif
 #ifndef NORM_C2_NOTAIL
 #define NORM_C2_NOTAIL 0      // 1: whole H items only (the last one computes a few columns in vain) instead of the short item
 #endif
@@ -107,7 +110,8 @@ struct Fused2Cfg {
     // H-pass outputs per thread.  The 4-channel H pass of the RGBA blur takes 10 where that fills the rounds of 128
     // threads (r = 21: 21 rows x 12 items = 252) and 8 where 8 does (r = 15, 17: 15 items per row give 225 / 255;
     // measured 146 vs 141 / 139 Gpixel/s).
-    static constexpr bool VSHIFT = NORM_C2_VSHIFT && !NORM_C2_CPAIR && R >= (MODE == 0 ? (GRAY ? NORM_C2_VSHIFT_MINR0G : NORM_C2_VSHIFT_MINR0) : NORM_C2_VSHIFT_MINR1);
+    static constexpr bool VSHIFT = NORM_C2_VSHIFT && !NORM_C2_CPAIR && R >= (MODE == 0 ? (GRAY ? NORM_C2_VSHIFT_MINR0G : NORM_C2_VSHIFT_MINR0) : NORM_C2_VSHIFT_MINR1) &&
+                                   !(NORM_C2_ROT21 && MODE == 0 && !GRAY && R == 21);
     // RGB chain at the largest radii: 3 x (R - 1) running outputs (114 at r = 39) exceed what a thread of group B can
     // hold when two CTAs share an SM (3 x 80 registers per thread trio).  Those radii run ONE CTA per SM with up to 168
     // registers per thread and no re-division, and spend the freed shared memory and registers on longer batches and
