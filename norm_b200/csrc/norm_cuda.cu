@@ -23,6 +23,7 @@
 #include "filter_kernels.cuh"
 #include "overlay_kernels.cuh"
 #include "stencil_kernels.cuh"
+#include "chainw_kernels.cuh"
 #include "stage_kernels.cuh"
 #include "unfilter_kernels.cuh"
 
@@ -84,6 +85,7 @@ struct norm_ctx {
     uint32_t force_bands = 0;    // NORM_CUDA_BANDS: row bands per frame of the fused kernels (experiments)
     size_t chunk_bytes = 0;      // NORM_CUDA_CHUNK_BYTES: frames per chunk of the staged paths (tests: many small chunks)
     int fused_gen = 0;           // NORM_CUDA_FUSED_GEN=1 forces the first-generation fused kernel
+    int win3 = 1;                // NORM_CUDA_WIN3=0: the chain at r = 3 runs the pipelined kernel instead of the register-window kernel
     bool force_unfused = false;  // NORM_CUDA_FORCE_UNFUSED=1: run the chain as separate stage kernels
 };
 
@@ -658,12 +660,59 @@ norm_status try_launch_blur_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p,
     }
 }
 
+// The chain at r = 3 on register windows (chainw_kernels.cuh): one warp per tile of 120 columns x tile_rows rows.
+template <bool GRAY, bool FRONT>
+norm_status launch_chain_win3(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
+                              double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1) {
+    FusedParams fp;
+    std::memset(&fp, 0, sizeof(fp));
+    fp.in = in, fp.out = out;
+    if (make_taps(3, fp.taps) != NORM_OK || fp.taps.n != 3 || fp.taps.dmin != -1) return fail(ctx, NORM_E_INVALID_ARG, "bad radius");
+    fp.lut = p.lut;
+    fp.out_y0 = slot.win_y1 ? slot.win_y0 : 0u;
+    fp.out_y1 = slot.win_y1 ? std::min(slot.win_y1, in.h) : in.h;
+    if (fp.out_y0 >= fp.out_y1) return fail(ctx, NORM_E_INVALID_ARG, "empty output row window");
+    const uint32_t out_rows = fp.out_y1 - fp.out_y0;
+    fp.invert = p.inv ? 1u : 0u;
+    fp.do_ssim = (d_ssim || d_moments) ? 1u : 0u;
+    fp.ssim_y0 = std::max(y0, fp.out_y0), fp.ssim_y1 = std::max(fp.ssim_y0, std::min(y1, fp.out_y1));
+    // tile height: 72 rows (4 of 76 source rows are halo) when that still gives every warp of the grid two tiles,
+    // halved down to 18 for small jobs
+    const uint32_t tiles_x = (in.w + kCwCols - 1) / kCwCols;
+    const size_t want = (size_t)ctx->sm_count * 2 * kCwWarps * 2;
+    uint32_t tile_rows = 72;
+    while (tile_rows > 18 && (size_t)tiles_x * ((out_rows + tile_rows - 1) / tile_rows) * in.frames < want) tile_rows /= 2;
+    const uint32_t tiles_y = (out_rows + tile_rows - 1) / tile_rows;
+    const size_t tiles = (size_t)tiles_x * tiles_y * in.frames;
+    if (tiles >= (1ull << 31)) return fail(ctx, NORM_E_UNSUPPORTED, "more than 2^31 work items in one launch: split the batch");
+    const uint32_t items_per_frame = tiles_x * tiles_y;
+    if (fp.do_ssim) {
+        NORM_TRY(ensure_buf(ctx, slot.partials, (size_t)in.frames * items_per_frame * 5 * sizeof(double)));
+        fp.partials = static_cast<double *>(slot.partials.p);
+    }
+    const unsigned grid = grid_for(ctx, (tiles + kCwWarps - 1) / kCwWarps, 2);
+    chain_win3_kernel<GRAY, FRONT><<<grid, kCwThreads, 0, slot.stream>>>(fp, tiles_x, tiles_y, tile_rows);
+    LAUNCH_CHECK(ctx);
+    if (fp.do_ssim) {
+        const double npix = (double)in.w * (double)(fp.ssim_y1 - fp.ssim_y0);
+        ssim_finalize_kernel<<<in.frames, 256, 0, slot.stream>>>(fp.partials, items_per_frame, npix, d_moments, d_ssim,
+                                                                 slot.accumulate ? 1 : 0);
+        LAUNCH_CHECK(ctx);
+    }
+    return NORM_OK;
+}
+
 norm_status try_launch_chain_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in,
                                    const ImgView &out, double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1,
                                    bool *fused) {
     *fused = false;
     if (!(p.blur && p.edge) || p.sharpen || ctx->force_unfused) return NORM_OK;
     *fused = true;
+    if (p.radius == 3 && ctx->win3 && ctx->fused_gen != 1) {
+        if (p.gray) return launch_chain_win3<true, true>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+        if (p.front) return launch_chain_win3<false, true>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+        return launch_chain_win3<false, false>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+    }
     switch (p.radius) {
     case 3: return launch_fused_r<3>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
     case 7: return launch_fused_r<7>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
@@ -780,6 +829,7 @@ norm_status create_impl(int32_t device, void *ext_stream, bool use_ext, norm_ctx
     if (const char *e = std::getenv("NORM_CUDA_FORCE_UNFUSED")) ctx->force_unfused = e[0] == '1';
     if (const char *e = std::getenv("NORM_CUDA_FUSED_GEN")) ctx->fused_gen = std::atoi(e);
     if (const char *e = std::getenv("NORM_CUDA_BALANCED")) ctx->balanced_partition = std::atoi(e);
+    if (const char *e = std::getenv("NORM_CUDA_WIN3")) ctx->win3 = std::atoi(e);
     if (const char *e = std::getenv("NORM_CUDA_BANDS")) ctx->force_bands = (uint32_t)std::atoi(e);
     if (const char *e = std::getenv("NORM_CUDA_CHUNK_BYTES")) ctx->chunk_bytes = (size_t)std::strtoull(e, nullptr, 10);
     auto bail = [&](cudaError_t ce, const char *what) {

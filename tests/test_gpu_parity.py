@@ -406,6 +406,43 @@ def test_balanced_partition_of_one_frame(oracle, monkeypatch):
                 src.destroy(), dst.destroy()
 
 
+def test_chain_r3_window_kernel_ragged(oracle, monkeypatch):
+    """The chain at r = 3 runs chain_win3_kernel (register windows, one warp per 120-column tile): widths around the
+    tile and chunk boundaries, heights around the tile-row counts and the three-step unroll, every front-stage
+    combination, a batch -- against the oracle, and against the pipelined kernel (NORM_CUDA_WIN3=0)."""
+    sizes = [(1, 1), (2, 3), (3, 2), (4, 1), (5, 19), (119, 18), (120, 20), (121, 37), (123, 74), (240, 5), (243, 145), (1000, 77)]
+    kws = [dict(blur=1, blur_radius=3, edge_detect=1), dict(grayscale=1, blur=1, blur_radius=3, edge_detect=1),
+           dict(invert=1, gamma=45455, blur=1, blur_radius=3, edge_detect=1)]
+    results = {}
+    for win3 in ("1", "0"):
+        monkeypatch.setenv("NORM_CUDA_WIN3", win3)
+        with nb.Context(0) as c:
+            for (w, h) in sizes:
+                img = smooth_rgba(w, h, seed=3 * w + h)
+                for ki, kw in enumerate(kws):
+                    f = uniform(w, h, **kw)
+                    src, dst = c.image_from_host(img[None]), c.image_create(w, h, 1)
+                    s = c.chain(f, src, dst, nb.NORM_CS_RAW)
+                    got = dst.download()[0]
+                    if win3 == "1":
+                        eo, es = oracle.chain(img, oracle_uniform(oracle, f), oracle.CS_RAW)
+                        assert np.array_equal(got, eo), (w, h, kw)
+                        assert abs(s[0] - es) <= SSIM_TIGHT or (w * h == 1), (w, h, kw)
+                        results[(w, h, ki)] = (got, s[0])
+                    else:
+                        assert np.array_equal(got, results[(w, h, ki)][0]), (w, h, kw)
+                        assert abs(s[0] - results[(w, h, ki)][1]) <= SSIM_TIGHT or (w * h == 1)
+                    src.destroy(), dst.destroy()
+            if win3 == "1":  # a batch: tiles of several frames in one launch
+                frames = np.stack([smooth_rgba(250, 91, seed=70 + i) for i in range(5)])
+                f = uniform(250, 91, blur=1, blur_radius=3, edge_detect=1)
+                eo, es = oracle.chain_batch(frames, oracle_uniform(oracle, f), oracle.CS_RAW)
+                src, dst = c.image_from_host(frames), c.image_create(250, 91, 5)
+                s = c.chain(f, src, dst, nb.NORM_CS_RAW)
+                assert np.array_equal(dst.download(), eo) and np.abs(s - es).max() <= SSIM_TIGHT
+                src.destroy(), dst.destroy()
+
+
 def test_multi_chunk_paths_bit_exact(oracle, monkeypatch):
     """The chunk loops only large batches reach: the host pipeline's slot reuse (chunk index mod 3) and the unfused
     chain's ping-pong temporaries rotating across chunks.  NORM_CUDA_CHUNK_BYTES (read when a context is created)
@@ -593,7 +630,7 @@ def test_band_mode_emulated_ranks(ctx, oracle, nranks):
     w, h = 300, 211
     img = smooth_rgba(w, h, seed=31)
     for kw in (dict(blur=1, blur_radius=21, edge_detect=1), dict(grayscale=1, blur=1, blur_radius=7, edge_detect=1),
-               dict(blur=1, blur_radius=5, sharpen=1)):
+               dict(blur=1, blur_radius=5, sharpen=1), dict(blur=1, blur_radius=3, edge_detect=1)):
         f = uniform(w, h, **kw)
         lays = [nb.sharding.band_layout(f, h, nranks, r) for r in range(nranks)]
         bands = [ctx.image_create(w, l["ext_rows"], 1) for l in lays]
@@ -628,7 +665,8 @@ def test_band_scheduler_emulated_ranks(oracle, nranks):
     the oracle on the whole image.  Two steps in a row with changed source rows exercise begin_update / publish."""
     w = 300
     for kw, h in ((dict(blur=1, blur_radius=21, edge_detect=1), 211), (dict(grayscale=1, blur=1, blur_radius=7, edge_detect=1), 97),
-                  (dict(blur=1, blur_radius=5, sharpen=1), 64), (dict(blur=1, blur_radius=21, edge_detect=1), 40)):
+                  (dict(blur=1, blur_radius=5, sharpen=1), 64), (dict(blur=1, blur_radius=21, edge_detect=1), 40),
+                  (dict(blur=1, blur_radius=3, edge_detect=1), 131)):
         f = uniform(w, h, **kw)
         ctxs = [nb.Context(0) for _ in range(nranks)]
         bands = [nb.Band(c, f, w, h, nranks, r) for r, c in enumerate(ctxs)]
