@@ -43,7 +43,8 @@ __device__ __forceinline__ uint32_t unorm8_rn(float v) {
     return (uint32_t)__float2int_rn(__fmul_rn(v, 255.0f));
 }
 
-__device__ __forceinline__ uint32_t srgb_code(const float *thresh, float v) {
+// sRGB code of a linear value = the largest j with v >= thresh[j] (thresh[0] = -inf side: every v, NaN included, gives >= 0).
+__device__ __forceinline__ uint32_t srgb_code_search(const float *thresh, float v) {
     uint32_t lo = 0, hi = 255;
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
@@ -53,6 +54,17 @@ __device__ __forceinline__ uint32_t srgb_code(const float *thresh, float v) {
     }
     return lo;
 }
+// The same code from a first guess: guess[i] is the code of the value i / 4095, a lower bound for every v in that cell
+// (at most two codes short next to zero, where the curve is steepest), then stepped against the thresholds until it
+// is exact -- two dependent look-ups on average instead of eight.
+constexpr int kSrgbGuess = 4096;
+__device__ __forceinline__ uint32_t srgb_code(const float *thresh, const uint8_t *guess, float v) {
+    const int cell = min(max(__float2int_rd(__fmul_rn(v, (float)(kSrgbGuess - 1))), 0), kSrgbGuess - 1);  // NaN -> 0
+    uint32_t c = guess[cell];
+    while (c < 255u && v >= thresh[c + 1]) ++c;
+    while (c > 0u && v < thresh[c]) --c;  // (the cell index is a rounded product: it can land one cell high)
+    return c;
+}
 
 // Shape layer + composite + crosshair for the four pixels (x .. x+3, y) of one lane; (wbx, wby) is the warp's
 // 32 x 4 block, whose pixel-centre box drives the warp-uniform reach test.  Not inlined: the caller walks
@@ -60,7 +72,8 @@ __device__ __forceinline__ uint32_t srgb_code(const float *thresh, float v) {
 struct OverlayLists {
     const float *cx, *cy, *rp;
     const uint16_t *idx;
-    const float *eotf, *thresh;
+    const float *eotf, *thresh, *div255;  // div255[b] = b / 255 (IEEE division, tabulated once per CTA)
+    const uint8_t *guess;
     uint32_t cnt, selected;
     bool cross;
     float mx, my, mr;
@@ -69,7 +82,8 @@ struct OverlayLists {
 
 __device__ __noinline__ uint4 overlay_shade(uint4 src, int x, int y, int wbx, int wby, const OverlayLists &L) {
     uint32_t px[4] = {src.x, src.y, src.z, src.w};
-    const float *s_cx = L.cx, *s_cy = L.cy, *s_rp = L.rp, *s_eotf = L.eotf, *s_thresh = L.thresh;
+    const float *s_cx = L.cx, *s_cy = L.cy, *s_rp = L.rp, *s_eotf = L.eotf, *s_thresh = L.thresh, *s_div = L.div255;
+    const uint8_t *s_guess = L.guess;
     const uint16_t *s_idx = L.idx;
     const uint32_t cnt = L.cnt, selected = L.selected;
     const bool cross = L.cross;
@@ -129,12 +143,12 @@ __device__ __noinline__ uint4 overlay_shade(uint4 src, int x, int y, int wbx, in
             if (ca == 0 && !hit) continue;
             float p[4];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) p[c] = __fdiv_rn(byte_f(px[j], c), 255.0f);
+            for (int c = 0; c < 4; ++c) p[c] = s_div[(px[j] >> (8 * c)) & 0xffu];
             if (ca > 0) {
-                const float sa = __fdiv_rn((float)ca, 255.0f);
-                p[0] = mix_rn(p[0], s_eotf[srgb_code(s_thresh, __fmul_rn(c0[j], c3[j]))], sa);
-                p[1] = mix_rn(p[1], s_eotf[srgb_code(s_thresh, __fmul_rn(c1[j], c3[j]))], sa);
-                p[2] = mix_rn(p[2], s_eotf[srgb_code(s_thresh, __fmul_rn(c2[j], c3[j]))], sa);
+                const float sa = s_div[ca];
+                p[0] = mix_rn(p[0], s_eotf[srgb_code(s_thresh, s_guess, __fmul_rn(c0[j], c3[j]))], sa);
+                p[1] = mix_rn(p[1], s_eotf[srgb_code(s_thresh, s_guess, __fmul_rn(c1[j], c3[j]))], sa);
+                p[2] = mix_rn(p[2], s_eotf[srgb_code(s_thresh, s_guess, __fmul_rn(c2[j], c3[j]))], sa);
                 p[3] = mix_rn(p[3], sa, sa);
             }
             if (hit) p[0] = 0.0f, p[1] = 1.0f, p[2] = 1.0f;
@@ -150,15 +164,19 @@ __global__ void __launch_bounds__(256) overlay_kernel(ImgView in, ImgView out, c
     __shared__ float s_cx[kMaxCircles], s_cy[kMaxCircles], s_rp[kMaxCircles];
     __shared__ uint16_t s_idx[kMaxCircles];
     __shared__ uint32_t s_warp_cnt[8];
-    __shared__ float s_eotf[256], s_thresh[256];
+    __shared__ float s_eotf[256], s_thresh[256], s_div255[256];
+    __shared__ uint8_t s_guess[kSrgbGuess];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     s_eotf[tid] = tab.eotf[tid];
     s_thresh[tid] = tab.thresh[tid];
+    s_div255[tid] = __fdiv_rn((float)tid, 255.0f);
+    __syncthreads();
+    for (int i = tid; i < kSrgbGuess; i += 256) s_guess[i] = (uint8_t)srgb_code_search(s_thresh, __fdiv_rn((float)i, (float)(kSrgbGuess - 1)));
     const uint32_t n = op.num_circles, selected = op.selected;
     const bool cross = op.crosshair == 1u;
     const float mx = op.mx, my = op.my, mr = op.mr;
     __shared__ OverlayLists lists;  // read by overlay_shade(); in shared memory so the callee's loads are cheap
-    if (tid == 0) lists = OverlayLists{s_cx, s_cy, s_rp, s_idx, s_eotf, s_thresh, 0u, selected, cross, mx, my, mr, (int)in.w, (int)in.h};
+    if (tid == 0) lists = OverlayLists{s_cx, s_cy, s_rp, s_idx, s_eotf, s_thresh, s_div255, s_guess, 0u, selected, cross, mx, my, mr, (int)in.w, (int)in.h};
     const uint32_t tiles_per_frame = tiles_x * tiles_y;
     const size_t total = (size_t)tiles_per_frame * in.frames;
     for (size_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
