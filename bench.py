@@ -186,9 +186,11 @@ def run_reference_arm(args, rank):
 
 def pcie_ceilings(torch, dev, barrier, nbytes=1 << 30):
     """Pinned-memory copy rates of this rank's GPU, GB/s: H2D alone, D2H alone, both at once (each direction's rate).
-    Every repetition starts behind a barrier over the ranks and the SLOWEST of three is reported, so at N > 1 the figure
-    is the rate with all GPUs of the box copying at once (they share the host's memory and PCIe root ports) - the
-    ceiling the end-to-end path of N ranks actually has."""
+    Every repetition starts behind a barrier over the ranks, so at N > 1 the figure is the rate with all GPUs of the box
+    copying at once (they share the host's memory and PCIe root ports) - the ceiling the end-to-end path of N ranks
+    actually has.  The FASTEST of three repetitions is reported per rank (a ceiling is the best the links did; with the
+    slowest, the pipelined end-to-end path measured 8 % above its own "ceiling" at N = 8) and the caller takes the
+    minimum over the ranks, since the step time is the slowest rank's."""
     h_in = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
     h_out = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
     d_a = torch.empty(nbytes, dtype=torch.uint8, device=dev)
@@ -196,7 +198,7 @@ def pcie_ceilings(torch, dev, barrier, nbytes=1 << 30):
     s1, s2 = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
 
     def run(h2d, d2h, reps=3):
-        best = 0.0
+        best = float("inf")
         for rep in range(reps + 1):
             barrier()
             t0 = time.perf_counter()
@@ -208,10 +210,10 @@ def pcie_ceilings(torch, dev, barrier, nbytes=1 << 30):
                     h_out.copy_(d_b, non_blocking=True)
             torch.cuda.synchronize()
             if rep:  # (the first repetition warms the path up)
-                best = max(best, time.perf_counter() - t0)
+                best = min(best, time.perf_counter() - t0)
         return nbytes / best / 1e9
     out = {"h2d_gbs": run(True, False), "d2h_gbs": run(False, True), "both_each_direction_gbs": run(True, True),
-           "bytes": nbytes, "how": "torch pinned <-> device copies of 1 GiB, all ranks at once behind a barrier, slowest of 3, wall clock around a device sync"}
+           "bytes": nbytes, "how": "torch pinned <-> device copies of 1 GiB, all ranks at once behind a barrier, fastest of 3 (then the minimum over ranks), wall clock around a device sync"}
     del h_in, h_out, d_a, d_b
     return out
 
