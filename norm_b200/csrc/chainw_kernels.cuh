@@ -28,11 +28,11 @@ __global__ void __launch_bounds__(kCwThreads, 2) chain_win3_kernel(const __grid_
                                                             uint32_t tile_rows) {
     constexpr int CH = GRAY ? 1 : 3;                       // after grayscale the three colour channels coincide
     constexpr int FR = (FRONT ? 1 : 0) | (GRAY ? 2 : 0);   // s3_front: bit 0 table, bit 1 grayscale
-    __shared__ float lumaLut[256];
+    __shared__ double lumaLutD[256];  // luma of the output pixel (c, c, c), as the f64 the moments take
     __shared__ uint8_t slut[256];
     for (int i = threadIdx.x; i < 256; i += kCwThreads) {
         const float c = (float)i;
-        lumaLut[i] = __fadd_rn(__fadd_rn(__fmul_rn(c, kLumaR), __fmul_rn(c, kLumaG)), __fmul_rn(c, kLumaB));
+        lumaLutD[i] = (double)__fadd_rn(__fadd_rn(__fmul_rn(c, kLumaR), __fmul_rn(c, kLumaG)), __fmul_rn(c, kLumaB));
         slut[i] = p.lut.v[i];
     }
     __syncthreads();
@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(kCwThreads, 2) chain_win3_kernel(const __grid_
             }
             uint32_t px[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) l.v[j] = luma_ssim(q.p[j]), px[j] = s3_front<FR>(q.p[j], slut, inv_mask);
+            for (int j = 0; j < 4; ++j) l.v[j] = luma_ssim(q.p[j]), px[j] = FR == 0 ? q.p[j] : s3_front<FR>(q.p[j], slut, inv_mask);  // (no front stage, no inversion either)
 #pragma unroll
             for (int c = 0; c < CH; ++c) {
                 float v[6];
@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(kCwThreads, 2) chain_win3_kernel(const __grid_
         }                                                                                                         \
         if (srow) { /* warp-uniform; lanes that own no pixel accumulate too and are cleared at the end of the tile */ \
             _Pragma("unroll") for (int j = 0; j < 4; ++j) {                                                       \
-                double xv = (double)lumaLut[cbs[j] & 0xffu], yv = (double)LN.v[j];                                \
+                double xv = lumaLutD[cbs[j] & 0xffu], yv = (double)LN.v[j];                                \
                 if (border_tile && col + j >= W) xv = 0.0, yv = 0.0;                                              \
                 m5[0] += xv;                                                                                      \
                 m5[1] += yv;                                                                                      \
