@@ -216,4 +216,127 @@ __global__ void __launch_bounds__(kCwThreads, 2) chain_win3_kernel(const __grid_
     }
 }
 
+
+// The blur alone at r = 3 (norm_cuda_blur, the blur effect of norm_cuda_effects; image_shader.wgsl:88-103 blurs all four
+// channels) on the same register windows: no Sobel, no moments, so a step is unpack -> H pass -> V pass -> quantise ->
+// one 16-byte store, and the kernel runs at the memory system's pace instead of the pipelined kernel's hand-offs.
+// Channels travel as pairs (r, g) and (b, a) so that every tap is one FFMA2; after grayscale the pairs are (y, a) only.
+template <bool GRAY, bool FRONT>
+__global__ void __launch_bounds__(kCwThreads, 2) blur_win3_kernel(const __grid_constant__ FusedParams p, uint32_t tiles_x, uint32_t tiles_y,
+                                                                  uint32_t tile_rows) {
+    constexpr int NP = GRAY ? 1 : 2;                       // channel pairs: (y, a) after grayscale, else (r, g) and (b, a)
+    constexpr int FR = (FRONT ? 1 : 0) | (GRAY ? 2 : 0);
+    __shared__ uint8_t slut[256];
+    for (int i = threadIdx.x; i < 256; i += kCwThreads) slut[i] = p.lut.v[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int W = (int)p.in.w, H = (int)p.in.h;
+    const float t0 = p.taps.t[0], t1 = p.taps.t[1], t2 = p.taps.t[2];
+    const float2 t0p = make_float2(t0, t0), t1p = make_float2(t1, t1), t2p = make_float2(t2, t2);
+    const uint32_t inv_mask = p.invert ? 0x00ffffffu : 0u;
+    const uint32_t tiles_per_frame = tiles_x * tiles_y;
+    const size_t total = (size_t)tiles_per_frame * p.in.frames;
+    const uint32_t ipitch = (uint32_t)p.in.pitch, opitch = (uint32_t)p.out.pitch;
+    struct Raw {
+        uint32_t p[4];
+    };
+    struct HRow {
+        float2 v[4][NP];  // H-pass outputs of this lane's four columns, per channel pair
+    };
+    const uint32_t steps = (tile_rows + 2) / 3 * 3;  // the same for every tile: the shuffles sit in uniform control flow
+
+    for (size_t tile = (size_t)blockIdx.x * kCwWarps + (threadIdx.x >> 5); tile < total; tile += (size_t)gridDim.x * kCwWarps) {
+        const uint32_t f = (uint32_t)(tile / tiles_per_frame);
+        const uint32_t tr = (uint32_t)(tile - (size_t)f * tiles_per_frame);
+        const int x0 = (int)(tr % tiles_x) * kCwCols;
+        const int ya = (int)p.out_y0 + (int)(tr / tiles_x) * (int)tile_rows, yb = min(ya + (int)tile_rows, (int)p.out_y1);
+        const int col = x0 - 4 + 4 * lane;
+        const bool vec = col >= 0 && col + 3 < W;
+        const bool writes = lane >= 1 && lane <= 30 && col < W;
+        const int colc = clampi(col, 0, ((W - 1) >> 2) << 2);
+        const bool border_tile = x0 == 0 || x0 + kCwCols + 4 > W;
+        const uint8_t *lbase = p.in.ptr + (size_t)f * p.in.frame_stride + (size_t)colc * 4;
+        uint8_t *obase = p.out.ptr + (size_t)f * p.out.frame_stride;
+        // step n: source row q = n + 2 of the clamped sequence row(q) = clamp(ya - 1 + q) arrives, output row ya + n leaves
+        auto fetch = [&](int q) {
+            const uint4 v = ldg_stream(reinterpret_cast<const uint4 *>(lbase + (uint64_t)(uint32_t)clampi(ya - 1 + q, 0, H - 1) * ipitch));
+            Raw r;
+            r.p[0] = v.x, r.p[1] = v.y, r.p[2] = v.z, r.p[3] = v.w;
+            return r;
+        };
+        auto hrow = [&](const Raw &rin, HRow &h) {
+            Raw q = rin;
+            if (border_tile && !vec) {  // ClampToEdge on the source columns
+                const int le = (W - 1) & 3;
+                const uint32_t last = le == 0 ? q.p[0] : le == 1 ? q.p[1] : le == 2 ? q.p[2] : q.p[3];
+                const uint32_t edge = col < 0 ? q.p[0] : last;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (col + j < 0 || col + j > W - 1) q.p[j] = edge;
+            }
+            float2 v[6][NP];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t px = FR == 0 ? q.p[j] : s3_front<FR>(q.p[j], slut, inv_mask);
+                if (GRAY) {
+                    v[1 + j][0] = make_float2(byte_f(px, 0), byte_f(px, 3));
+                } else {
+                    v[1 + j][0] = make_float2(byte_f(px, 0), byte_f(px, 1));
+                    v[1 + j][NP - 1] = make_float2(byte_f(px, 2), byte_f(px, 3));
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < NP; ++c) {
+                v[0][c].x = __shfl_up_sync(0xffffffffu, v[4][c].x, 1), v[0][c].y = __shfl_up_sync(0xffffffffu, v[4][c].y, 1);
+                v[5][c].x = __shfl_down_sync(0xffffffffu, v[1][c].x, 1), v[5][c].y = __shfl_down_sync(0xffffffffu, v[1][c].y, 1);
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    h.v[j][c] = __ffma2_rn(t2p, v[j + 2][c], __ffma2_rn(t1p, v[j + 1][c], __fmul2_rn(t0p, v[j][c])));
+            }
+        };
+        Raw r0 = fetch(0), r1 = fetch(1), r2 = fetch(2);
+        HRow ha, hb, hc;
+        hrow(r0, ha);
+        r0 = fetch(3);
+        hrow(r1, hb);
+        r1 = fetch(4);
+#define BW_STEP(N_, RC, HA, HB, HC)                                                                               \
+    {                                                                                                             \
+        const int n_ = (N_), y_ = ya + n_;                                                                        \
+        hrow(RC, HC);                                                                                             \
+        RC = fetch(n_ + 5);                                                                                       \
+        uint32_t o[4];                                                                                            \
+        _Pragma("unroll") for (int j = 0; j < 4; ++j) {                                                           \
+            uint32_t qb[NP][2];                                                                                   \
+            _Pragma("unroll") for (int c = 0; c < NP; ++c) {                                                      \
+                const float2 b = __ffma2_rn(t2p, HC.v[j][c], __ffma2_rn(t1p, HB.v[j][c], __fmul2_rn(t0p, HA.v[j][c]))); \
+                qb[c][0] = __float_as_uint(__fadd_rn(b.x, 12582912.0f));                                          \
+                qb[c][1] = __float_as_uint(__fadd_rn(b.y, 12582912.0f));                                          \
+            }                                                                                                     \
+            if (GRAY) { /* (y, y, y, a) */                                                                        \
+                o[j] = __byte_perm(qb[0][0], qb[0][1], 0x4000);                                                   \
+            } else {   /* low bytes of the four biased sums -> (r, g, b, a) */                                    \
+                o[j] = __byte_perm(__byte_perm(qb[0][0], qb[0][1], 0x7740), __byte_perm(qb[NP - 1][0], qb[NP - 1][1], 0x7740), 0x5410); \
+            }                                                                                                     \
+        }                                                                                                         \
+        if (y_ < yb && writes) {                                                                                  \
+            uint8_t *orow = obase + (uint64_t)(uint32_t)y_ * opitch;                                              \
+            if (vec) {                                                                                            \
+                stg_stream(reinterpret_cast<uint4 *>(orow + (size_t)col * 4), make_uint4(o[0], o[1], o[2], o[3])); \
+            } else {                                                                                              \
+                _Pragma("unroll") for (int j = 0; j < 4; ++j) if (col + j < W)                                    \
+                        reinterpret_cast<uint32_t *>(orow)[col + j] = o[j];                                       \
+            }                                                                                                     \
+        }                                                                                                         \
+    }
+#pragma unroll 1
+        for (int n = 0; n < (int)steps; n += 3) {
+            BW_STEP(n, r2, ha, hb, hc)
+            BW_STEP(n + 1, r0, hb, hc, ha)
+            BW_STEP(n + 2, r1, hc, ha, hb)
+        }
+#undef BW_STEP
+    }
+}
+
 }  // namespace normk

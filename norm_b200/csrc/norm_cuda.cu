@@ -85,7 +85,7 @@ struct norm_ctx {
     uint32_t force_bands = 0;    // NORM_CUDA_BANDS: row bands per frame of the fused kernels (experiments)
     size_t chunk_bytes = 0;      // NORM_CUDA_CHUNK_BYTES: frames per chunk of the staged paths (tests: many small chunks)
     int fused_gen = 0;           // NORM_CUDA_FUSED_GEN=1 forces the first-generation fused kernel
-    int win3 = 1;                // NORM_CUDA_WIN3=0: the chain at r = 3 runs the pipelined kernel instead of the register-window kernel
+    int win3 = 1;                // NORM_CUDA_WIN3=0: chain and blur at r = 3 run the pipelined kernel instead of the register-window kernels
     bool force_unfused = false;  // NORM_CUDA_FORCE_UNFUSED=1: run the chain as separate stage kernels
 };
 
@@ -644,10 +644,42 @@ norm_status launch_blur_only_r(norm_ctx *ctx, Slot &slot, const StagePlan &p, co
     return NORM_OK;
 }
 
+// The blur alone at r = 3 on register windows (blur_win3_kernel).
+template <bool GRAY, bool FRONT>
+norm_status launch_blur_win3(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out) {
+    FusedParams fp;
+    std::memset(&fp, 0, sizeof(fp));
+    fp.in = in, fp.out = out;
+    if (make_taps(3, fp.taps) != NORM_OK || fp.taps.n != 3 || fp.taps.dmin != -1) return fail(ctx, NORM_E_INVALID_ARG, "bad radius");
+    fp.lut = p.lut;
+    fp.out_y0 = slot.win_y1 ? slot.win_y0 : 0u;
+    fp.out_y1 = slot.win_y1 ? std::min(slot.win_y1, in.h) : in.h;
+    if (fp.out_y0 >= fp.out_y1) return fail(ctx, NORM_E_INVALID_ARG, "empty output row window");
+    const uint32_t out_rows = fp.out_y1 - fp.out_y0;
+    fp.invert = p.inv ? 1u : 0u;
+    const uint32_t tiles_x = (in.w + kCwCols - 1) / kCwCols;
+    const size_t want = (size_t)ctx->sm_count * 2 * kCwWarps * 2;
+    uint32_t tile_rows = 72;  // 2 of 74 source rows are halo; halved down to 18 rows for small jobs
+    while (tile_rows > 18 && (size_t)tiles_x * ((out_rows + tile_rows - 1) / tile_rows) * in.frames < want) tile_rows /= 2;
+    const uint32_t tiles_y = (out_rows + tile_rows - 1) / tile_rows;
+    const size_t tiles = (size_t)tiles_x * tiles_y * in.frames;
+    if (tiles >= (1ull << 31)) return fail(ctx, NORM_E_UNSUPPORTED, "more than 2^31 work items in one launch: split the batch");
+    const unsigned grid = grid_for(ctx, (tiles + kCwWarps - 1) / kCwWarps, 2);
+    blur_win3_kernel<GRAY, FRONT><<<grid, kCwThreads, 0, slot.stream>>>(fp, tiles_x, tiles_y, tile_rows);
+    LAUNCH_CHECK(ctx);
+    return NORM_OK;
+}
+
 norm_status try_launch_blur_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
                                   bool *fused) {
     *fused = false;
     if (!p.blur || p.edge || p.sharpen || ctx->force_unfused || ctx->fused_gen == 1) return NORM_OK;
+    if (p.radius == 3 && ctx->win3) {
+        *fused = true;
+        if (p.gray) return launch_blur_win3<true, true>(ctx, slot, p, in, out);
+        if (p.front) return launch_blur_win3<false, true>(ctx, slot, p, in, out);
+        return launch_blur_win3<false, false>(ctx, slot, p, in, out);
+    }
     switch (p.radius) {
     case 3: return launch_blur_only_r<3>(ctx, slot, p, in, out, fused);
     case 7: return launch_blur_only_r<7>(ctx, slot, p, in, out, fused);

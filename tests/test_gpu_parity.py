@@ -407,12 +407,14 @@ def test_balanced_partition_of_one_frame(oracle, monkeypatch):
 
 
 def test_chain_r3_window_kernel_ragged(oracle, monkeypatch):
-    """The chain at r = 3 runs chain_win3_kernel (register windows, one warp per 120-column tile): widths around the
-    tile and chunk boundaries, heights around the tile-row counts and the three-step unroll, every front-stage
+    """The chain at r = 3 runs chain_win3_kernel and the blur alone blur_win3_kernel (register windows, one warp per
+    120-column tile): widths around the tile and chunk boundaries, heights around the tile-row counts and the three-step unroll, every front-stage
     combination, a batch -- against the oracle, and against the pipelined kernel (NORM_CUDA_WIN3=0)."""
     sizes = [(1, 1), (2, 3), (3, 2), (4, 1), (5, 19), (119, 18), (120, 20), (121, 37), (123, 74), (240, 5), (243, 145), (1000, 77)]
     kws = [dict(blur=1, blur_radius=3, edge_detect=1), dict(grayscale=1, blur=1, blur_radius=3, edge_detect=1),
-           dict(invert=1, gamma=45455, blur=1, blur_radius=3, edge_detect=1)]
+           dict(invert=1, gamma=45455, blur=1, blur_radius=3, edge_detect=1),
+           # the blur alone (blur_win3_kernel: all four channels; two after grayscale)
+           dict(blur=1, blur_radius=3), dict(grayscale=1, blur=1, blur_radius=3), dict(invert=1, gamma=250000, blur=1, blur_radius=3)]
     results = {}
     for win3 in ("1", "0"):
         monkeypatch.setenv("NORM_CUDA_WIN3", win3)
