@@ -445,6 +445,30 @@ def test_chain_r3_window_kernel_ragged(oracle, monkeypatch):
                 src.destroy(), dst.destroy()
 
 
+def test_large_radius_configurations_ragged(oracle, monkeypatch):
+    """The shift-form V pass and the one-CTA-per-SM configurations (RGB chain r >= 33, RGBA blur r >= 37; 34- / 38-row
+    batches, 12- / 8-column H items) on sizes around their strip, batch and item boundaries, tiny images included, with
+    the static partition and with the balanced partition of one frame forced."""
+    sizes = [(1, 1), (7, 5), (119, 33), (121, 35), (130, 69), (241, 40), (500, 103)]
+    kws = [dict(blur=1, blur_radius=23, edge_detect=1), dict(blur=1, blur_radius=31, edge_detect=1),
+           dict(blur=1, blur_radius=33, edge_detect=1), dict(invert=1, blur=1, blur_radius=39, edge_detect=1),
+           dict(grayscale=1, blur=1, blur_radius=39, edge_detect=1), dict(blur=1, blur_radius=29), dict(blur=1, blur_radius=37),
+           dict(blur=1, blur_radius=39)]
+    for balanced in ("1", "2"):
+        monkeypatch.setenv("NORM_CUDA_BALANCED", balanced)
+        with nb.Context(0) as c:
+            for (w, h) in sizes:
+                img = smooth_rgba(w, h, seed=5 * w + h)
+                for kw in kws:
+                    f = uniform(w, h, **kw)
+                    src, dst = c.image_from_host(img[None]), c.image_create(w, h, 1)
+                    s = c.chain(f, src, dst, nb.NORM_CS_RAW)
+                    eo, es = oracle.chain(img, oracle_uniform(oracle, f), oracle.CS_RAW)
+                    assert np.array_equal(dst.download()[0], eo), (balanced, w, h, kw)
+                    assert abs(s[0] - es) <= SSIM_TIGHT or (w * h == 1), (balanced, w, h, kw)
+                    src.destroy(), dst.destroy()
+
+
 def test_multi_chunk_paths_bit_exact(oracle, monkeypatch):
     """The chunk loops only large batches reach: the host pipeline's slot reuse (chunk index mod 3) and the unfused
     chain's ping-pong temporaries rotating across chunks.  NORM_CUDA_CHUNK_BYTES (read when a context is created)
