@@ -77,6 +77,9 @@ constexpr int kC2Group = 128, kC2Threads = 3 * kC2Group;
 #ifndef NORM_C2_ROT21
 #define NORM_C2_ROT21 1       // the RGB chain at r = 21 keeps the rotation: its 21-row batch gives 252 H items = 98 % of group A's lanes (20 rows: 94 %); measured 134.3 vs 131.8 Gpixel/s
 #endif
+#ifndef NORM_C2_HG2_MAXR
+#define NORM_C2_HG2_MAXR 27   // RGBA blur: two H groups + one V group up to this radius (0: never); see Fused2Cfg::HG2
+#endif
 #ifndef NORM_C2_NOTAIL
 #define NORM_C2_NOTAIL 0      // 1: whole H items only (the last one computes a few columns in vain) instead of the short item
 #endif
@@ -144,13 +147,18 @@ struct Fused2Cfg {
     // shared) and group B runs the V pass of both and stores RGBA8.  MODE 1 on RGBA: group A runs the H pass
     // of all four channels and groups B and C the V pass of two channels each (2 x R running outputs), because
     // 4 x R running outputs do not fit one thread's registers.
-    static constexpr int HGROUPS = (MODE == 1 && GRAY) ? 2 : 1;
-    static constexpr int VGROUPS = (MODE == 1 && !GRAY) ? 2 : 1;
-    static constexpr int CH_A = (MODE == 1 && GRAY) ? 1 : CH;   // channels of group A's H pass (from 0)
+    // RGBA blur up to r = NORM_C2_HG2_MAXR: the H pass of four channels is twice the V pass of two, so with "A = H, B and
+    // C = V of two channels each" groups B and C idle half the time.  Where 4 x (R - 1) running outputs fit one thread
+    // (112 registers), groups A and C run the H pass of two channels each and group B the V pass of all four.
+    static constexpr bool HG2 = NORM_C2_HG2_MAXR > 0 && MODE == 1 && !GRAY && VSHIFT && !BIG && R <= NORM_C2_HG2_MAXR;
+    static constexpr int HGROUPS = (MODE == 1 && (GRAY || HG2)) ? 2 : 1;
+    static constexpr int VGROUPS = (MODE == 1 && !GRAY && !HG2) ? 2 : 1;
+    static constexpr int CH_A = (MODE == 1 && GRAY) ? 1 : HG2 ? 2 : CH;   // channels of group A's H pass (from 0)
+    static constexpr int CH_C = HG2 ? 2 : 1;                              // channels of group C's H pass (the last ones)
     static constexpr int HTHREADS = HGROUPS * 128;
     // register budgets (setmaxnreg), summing to 3 x 80
-    static constexpr int REGS_H = BIG ? 168 : MODE == 1 ? (GRAY ? 56 : NORM_C2_REGS_H4) : NORM_C2_REGS_A;              // MODE 1 + GRAY: two H groups
-    static constexpr int REGS_V = BIG ? 168 : MODE == 1 ? (GRAY ? 128 : (240 - NORM_C2_REGS_H4) / 2) : NORM_C2_REGS_B;
+    static constexpr int REGS_H = BIG ? 168 : HG2 ? (R > 23 ? 56 : 64) : MODE == 1 ? (GRAY ? 56 : NORM_C2_REGS_H4) : NORM_C2_REGS_A;              // MODE 1 + GRAY: two H groups
+    static constexpr int REGS_V = BIG ? 168 : HG2 ? (R > 23 ? 128 : 112) : MODE == 1 ? (GRAY ? 128 : (240 - NORM_C2_REGS_H4) / 2) : NORM_C2_REGS_B;
     static constexpr int REGS_C = BIG ? 168 : MODE == 0 ? 240 - REGS_H - REGS_V : 0;
     // source byte of channel c: MODE 1 + GRAY blurs (y, alpha) = bytes (0, 3)
     __host__ __device__ static constexpr int chan_byte(int c) { return (MODE == 1 && GRAY && c == 1) ? 3 : c; }
@@ -235,14 +243,16 @@ __device__ __forceinline__ void v_pass_batch(const FusedParams &p, const float *
             if constexpr (GRAY) {
                 st_global_pred_u32(px, q0[0] * 0x010101u | (q0[NCH - 1] << 24), v0);
                 st_global_pred_u32(px + p.out.pitch, q1[0] * 0x010101u | (q1[NCH - 1] << 24), v1);
+            } else if constexpr (NCH == 4) {  // all four bytes of the pixel
+                st_global_pred_u32(px, q0[0] | (q0[1] << 8) | (q0[2] << 16) | (q0[3] << 24), v0);
+                st_global_pred_u32(px + p.out.pitch, q1[0] | (q1[1] << 8) | (q1[2] << 16) | (q1[3] << 24), v1);
             } else {
-                static_assert(NCH == 2, "RGBA: two channels per V-pass thread");
+                static_assert(NCH == 2, "RGBA: two or four channels per V-pass thread");
                 st_global_pred_u16(px + C0, q0[0] | (q0[1] << 8), v0);
                 st_global_pred_u16(px + p.out.pitch + C0, q1[0] | (q1[1] << 8), v1);
             }
         }
-        return;
-    }
+    } else {
 #pragma unroll
     for (int j = 0; j < C::RB; ++j) {
         uint32_t q[NCH];
@@ -283,6 +293,7 @@ __device__ __forceinline__ void v_pass_batch(const FusedParams &p, const float *
             st_global_pred_u16(px + C0, q[0] | (q[1] << 8), valid);
         }
     }
+    }  // rotation
 }
 
 // Blur-only consumer (MODE 1, group B): V pass for channels [C0, C0+NCH) of one blurred column per thread.
@@ -387,8 +398,8 @@ __global__ void __launch_bounds__(kC2Threads, (Fused2Cfg<R, GRAY, MODE>::CTAS)) 
     // ROLE 0 = group A: channels [0, CH_A).  ROLE 1 = group C in MODE 1 after grayscale: the alpha channel.
     auto h_group = [&](auto role_tag) {
         constexpr int ROLE = decltype(role_tag)::value;
-        constexpr int c0 = ROLE == 0 ? 0 : C::CH - 1;
-        constexpr int NCHH = ROLE == 0 ? C::CH_A : 1;
+        constexpr int c0 = ROLE == 0 ? 0 : C::CH - C::CH_C;
+        constexpr int NCHH = ROLE == 0 ? C::CH_A : C::CH_C;
         if constexpr (!C::BIG) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(C::REGS_H));
         constexpr int kHT = C::HTHREADS;
         const int hid = tid < kC2Group ? tid : tid - kC2Group;  // index within the H-pass threads
@@ -545,7 +556,7 @@ __global__ void __launch_bounds__(kC2Threads, (Fused2Cfg<R, GRAY, MODE>::CTAS)) 
         // =========================== group B: V pass + quantise + intensity ===========================
         if constexpr (MODE == 1) {
             if constexpr (!C::BIG) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REGS_V));
-            blur_only_consumer<C, R, GRAY, 0, 2, kABParties>(p, Hb_base, tid - kC2Group, items_per_frame, C2_TOTAL_ITEMS());
+            blur_only_consumer<C, R, GRAY, 0, (C::HG2 ? 4 : 2), kABParties>(p, Hb_base, tid - kC2Group, items_per_frame, C2_TOTAL_ITEMS());
             return;
         }
         if constexpr (!C::BIG) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REGS_V));
