@@ -102,7 +102,8 @@ static_assert(NORM_C2_REGS_A + NORM_C2_REGS_B + NORM_C2_REGS_C == 240, "register
 // MODE 1: front -> blur                     all four channels are blurred (image_shader.wgsl:88-103 blurs
 //         alpha too); after grayscale the three colour channels coincide, so two distinct channels (y, a)
 //         remain: groups A and C both run the H pass (one channel each, staging shared) and group B the V
-//         pass of both.  On RGBA group A runs the H pass of all four channels, B and C the V pass of two each.
+//         pass of both.  On RGBA up to r = 27 likewise: groups A and C run the H pass of two channels each, group B the V
+//         pass of all four (Fused2Cfg::HG2); above, group A runs the H pass of all four channels, B and C the V pass of two each.
 template <int R, bool GRAY, int MODE = 0>
 struct Fused2Cfg {
     static_assert(R % 2 == 1, "odd radii");
