@@ -23,11 +23,11 @@ constexpr int kCwCols = 120;  // output columns per warp tile (lanes 1..30 x 4 p
 #endif
 constexpr int kCwWarps = NORM_CW_WARPS, kCwThreads = 32 * kCwWarps;
 
-template <bool GRAY, bool FRONT>
+template <bool GRAY, int FRONT>  // FRONT: 0 no front stage, 1 with the 256-entry table, 2 grayscale / inversion without a table
 __global__ void __launch_bounds__(kCwThreads, 2) chain_win3_kernel(const __grid_constant__ FusedParams p, uint32_t tiles_x, uint32_t tiles_y,
                                                             uint32_t tile_rows) {
     constexpr int CH = GRAY ? 1 : 3;                       // after grayscale the three colour channels coincide
-    constexpr int FR = (FRONT ? 1 : 0) | (GRAY ? 2 : 0);   // s3_front: bit 0 table, bit 1 grayscale
+    constexpr int FR = (FRONT == 1 ? 1 : 0) | (GRAY ? 2 : 0);   // s3_front: bit 0 table, bit 1 grayscale
     __shared__ double lumaLutD[256];  // luma of the output pixel (c, c, c), as the f64 the moments take
     __shared__ uint8_t slut[256];
     for (int i = threadIdx.x; i < 256; i += kCwThreads) {
@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(kCwThreads, 2) chain_win3_kernel(const __grid_
             }
             uint32_t px[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) l.v[j] = luma_ssim(q.p[j]), px[j] = FR == 0 ? q.p[j] : s3_front<FR>(q.p[j], slut, inv_mask);  // (no front stage, no inversion either)
+            for (int j = 0; j < 4; ++j) l.v[j] = luma_ssim(q.p[j]), px[j] = FRONT == 0 ? q.p[j] : s3_front<FR>(q.p[j], slut, inv_mask);  // (no front stage, no inversion either)
 #pragma unroll
             for (int c = 0; c < CH; ++c) {
                 float v[6];
@@ -221,11 +221,11 @@ __global__ void __launch_bounds__(kCwThreads, 2) chain_win3_kernel(const __grid_
 // channels) on the same register windows: no Sobel, no moments, so a step is unpack -> H pass -> V pass -> quantise ->
 // one 16-byte store, and the kernel runs at the memory system's pace instead of the pipelined kernel's hand-offs.
 // Channels travel as pairs (r, g) and (b, a) so that every tap is one FFMA2; after grayscale the pairs are (y, a) only.
-template <bool GRAY, bool FRONT>
+template <bool GRAY, int FRONT>  // FRONT: 0 no front stage, 1 with the 256-entry table, 2 grayscale / inversion without a table
 __global__ void __launch_bounds__(kCwThreads, 2) blur_win3_kernel(const __grid_constant__ FusedParams p, uint32_t tiles_x, uint32_t tiles_y,
                                                                   uint32_t tile_rows) {
     constexpr int NP = GRAY ? 1 : 2;                       // channel pairs: (y, a) after grayscale, else (r, g) and (b, a)
-    constexpr int FR = (FRONT ? 1 : 0) | (GRAY ? 2 : 0);
+    constexpr int FR = (FRONT == 1 ? 1 : 0) | (GRAY ? 2 : 0);
     __shared__ uint8_t slut[256];
     for (int i = threadIdx.x; i < 256; i += kCwThreads) slut[i] = p.lut.v[i];
     __syncthreads();
@@ -277,7 +277,7 @@ __global__ void __launch_bounds__(kCwThreads, 2) blur_win3_kernel(const __grid_c
             float2 v[6][NP];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                const uint32_t px = FR == 0 ? q.p[j] : s3_front<FR>(q.p[j], slut, inv_mask);
+                const uint32_t px = FRONT == 0 ? q.p[j] : s3_front<FR>(q.p[j], slut, inv_mask);
                 if (GRAY) {
                     v[1 + j][0] = make_float2(byte_f(px, 0), byte_f(px, 3));
                 } else {

@@ -645,7 +645,7 @@ norm_status launch_blur_only_r(norm_ctx *ctx, Slot &slot, const StagePlan &p, co
 }
 
 // The blur alone at r = 3 on register windows (blur_win3_kernel).
-template <bool GRAY, bool FRONT>
+template <bool GRAY, int FRONT>
 norm_status launch_blur_win3(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out) {
     FusedParams fp;
     std::memset(&fp, 0, sizeof(fp));
@@ -676,9 +676,11 @@ norm_status try_launch_blur_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p,
     if (!p.blur || p.edge || p.sharpen || ctx->force_unfused || ctx->fused_gen == 1) return NORM_OK;
     if (p.radius == 3 && ctx->win3) {
         *fused = true;
-        if (p.gray) return launch_blur_win3<true, true>(ctx, slot, p, in, out);
-        if (p.front) return launch_blur_win3<false, true>(ctx, slot, p, in, out);
-        return launch_blur_win3<false, false>(ctx, slot, p, in, out);
+        // front stage: none / with the table / grayscale or inversion alone (the identity table is not looked up)
+        if (p.gray) return p.use_lut ? launch_blur_win3<true, 1>(ctx, slot, p, in, out) : launch_blur_win3<true, 2>(ctx, slot, p, in, out);
+        if (p.use_lut) return launch_blur_win3<false, 1>(ctx, slot, p, in, out);
+        if (p.front) return launch_blur_win3<false, 2>(ctx, slot, p, in, out);
+        return launch_blur_win3<false, 0>(ctx, slot, p, in, out);
     }
     switch (p.radius) {
     case 3: return launch_blur_only_r<3>(ctx, slot, p, in, out, fused);
@@ -693,7 +695,7 @@ norm_status try_launch_blur_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p,
 }
 
 // The chain at r = 3 on register windows (chainw_kernels.cuh): one warp per tile of 120 columns x tile_rows rows.
-template <bool GRAY, bool FRONT>
+template <bool GRAY, int FRONT>
 norm_status launch_chain_win3(norm_ctx *ctx, Slot &slot, const StagePlan &p, const ImgView &in, const ImgView &out,
                               double *d_ssim, double *d_moments, uint32_t y0, uint32_t y1) {
     FusedParams fp;
@@ -741,9 +743,12 @@ norm_status try_launch_chain_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p
     if (!(p.blur && p.edge) || p.sharpen || ctx->force_unfused) return NORM_OK;
     *fused = true;
     if (p.radius == 3 && ctx->win3 && ctx->fused_gen != 1) {
-        if (p.gray) return launch_chain_win3<true, true>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
-        if (p.front) return launch_chain_win3<false, true>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
-        return launch_chain_win3<false, false>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+        if (p.gray)
+            return p.use_lut ? launch_chain_win3<true, 1>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1)
+                             : launch_chain_win3<true, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+        if (p.use_lut) return launch_chain_win3<false, 1>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+        if (p.front) return launch_chain_win3<false, 2>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
+        return launch_chain_win3<false, 0>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
     }
     switch (p.radius) {
     case 3: return launch_fused_r<3>(ctx, slot, p, in, out, d_ssim, d_moments, y0, y1);
