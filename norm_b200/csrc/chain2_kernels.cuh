@@ -468,8 +468,8 @@ __global__ void __launch_bounds__(kC2Threads, (Fused2Cfg<R, GRAY, MODE>::CTAS)) 
                             uint32_t *pv = &v.x;
 #pragma unroll
                             for (int e = 0; e < 4; ++e) {
-                                uint32_t r = flut[pv[e] & 0xffu], gg = flut[(pv[e] >> 8) & 0xffu],
-                                         bb = flut[(pv[e] >> 16) & 0xffu];
+                                uint32_t r = pv[e] & 0xffu, gg = (pv[e] >> 8) & 0xffu, bb = (pv[e] >> 16) & 0xffu;
+                                if (!p.lut_identity) r = flut[r], gg = flut[gg], bb = flut[bb];  // (uniform branch)
                                 if (GRAY) {
                                     r = quant_u8(luma_fused((float)r, (float)gg, (float)bb));
                                     gg = bb = r;

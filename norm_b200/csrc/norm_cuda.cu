@@ -552,6 +552,7 @@ norm_status launch_fused(norm_ctx *ctx, Slot &slot, const StagePlan &p, const Im
         }
     }
     fp.invert = p.inv ? 1u : 0u;
+    fp.lut_identity = p.use_lut ? 0u : 1u;
     fp.do_ssim = (d_ssim || d_moments) ? 1u : 0u;
     fp.ssim_y0 = std::max(y0, fp.out_y0), fp.ssim_y1 = std::max(fp.ssim_y0, std::min(y1, fp.out_y1));
     if (grid_items >= (1ull << 31)) return fail(ctx, NORM_E_UNSUPPORTED, "more than 2^31 work items in one launch: split the batch");
